@@ -1,0 +1,310 @@
+"""CPU oracle for the ESRGAN hot path.  TEST INFRASTRUCTURE ONLY.
+
+This file is a functional, fp32, CPU restatement of the reference's algorithm
+(lukas-blecher/super-resolution).  Only ``tests/``, ``__graft_entry__.smoke()``
+and ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` legs may import it;
+the product (``super-resolution_b200/``) never does.
+
+Parity status: the reference has no tests or golden vectors of its own
+(SURVEY.md section 4), so formally "parity unpinned by the reference"; the
+oracle is pinned instead against outputs of the reference itself run in the
+build container (``tests/golden/make_golden.py`` imports /root/reference and
+writes ``tests/golden/*.pt``; ``tests/test_oracle_golden.py`` checks this file
+against them bit-for-bit-ish, tolerance 1e-6).
+
+Every function cites the reference file:line it restates.  The arithmetic is
+torch CPU fp32 (the reference's own numeric backend: ATen/oneDNN), written as
+explicit functional ops over a ``state_dict`` - no nn.Module from the
+reference is reused.  ``conv3x3_numpy`` is an independent numpy restatement of
+the convolution used to pin ``F.conv2d`` itself on small cases.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+Tensor = torch.Tensor
+SD = Dict[str, Tensor]
+
+G_LRELU_SLOPE = 0.01   # nn.LeakyReLU() default, models.py:21,88,98
+D_LRELU_SLOPE = 0.2    # nn.LeakyReLU(0.2), models.py:143,145
+DRB_RES_SCALE = 0.2    # DenseResidualBlock default; RRDB ctor never forwards res_scale (models.py:49)
+
+
+# ----------------------------------------------------------------------------
+# independent numpy convolution (pins F.conv2d on small cases)
+# ----------------------------------------------------------------------------
+def conv3x3_numpy(x: np.ndarray, w: np.ndarray, b: Optional[np.ndarray], stride: int = 1) -> np.ndarray:
+    """3x3, padding 1 cross-correlation, NCHW / OIHW, float64 accumulate.
+    Restates what nn.Conv2d(k=3, padding=1) computes (models.py:19,63,67,87,97,99,142,144)."""
+    B, C, H, W = x.shape
+    O = w.shape[0]
+    xp = np.zeros((B, C, H + 2, W + 2), dtype=np.float64)
+    xp[:, :, 1:-1, 1:-1] = x
+    Ho = (H + 2 - 3) // stride + 1
+    Wo = (W + 2 - 3) // stride + 1
+    out = np.zeros((B, O, Ho, Wo), dtype=np.float64)
+    for ky in range(3):
+        for kx in range(3):
+            patch = xp[:, :, ky:ky + stride * (Ho - 1) + 1:stride, kx:kx + stride * (Wo - 1) + 1:stride]
+            out += np.einsum("bchw,oc->bohw", patch, w[:, :, ky, kx].astype(np.float64))
+    if b is not None:
+        out += b.astype(np.float64)[None, :, None, None]
+    return out
+
+
+# ----------------------------------------------------------------------------
+# generator (models.py:9-135)
+# ----------------------------------------------------------------------------
+def dense_residual_block(sd: SD, prefix: str, x: Tensor) -> Tensor:
+    """models.py:34-41.  conv k sees concat(x, out_1..out_{k-1}); LeakyReLU(0.01)
+    after convs 1-4; returns out5 * 0.2 + x."""
+    inputs = x
+    out = x
+    for k in range(1, 6):
+        out = F.conv2d(inputs, sd[f"{prefix}b{k}.0.weight"], sd[f"{prefix}b{k}.0.bias"], 1, 1)
+        if k < 5:
+            out = F.leaky_relu(out, G_LRELU_SLOPE)
+        inputs = torch.cat([inputs, out], 1)
+    return out * DRB_RES_SCALE + x
+
+
+def rrdb(sd: SD, prefix: str, x: Tensor, res_scale: float) -> Tensor:
+    """models.py:44-53: three dense blocks, then * res_scale + x."""
+    out = x
+    for j in range(3):
+        out = dense_residual_block(sd, f"{prefix}dense_blocks.{j}.", out)
+    return out * res_scale + x
+
+
+def _count(sd: SD, pattern: str) -> int:
+    n = 0
+    while any(k.startswith(pattern % n) for k in sd):
+        n += 1
+    return n
+
+
+def generator_forward(sd: SD, x: Tensor, *, res_scale: float = 0.2, thres: float = 0.0,
+                      training: bool = True) -> Tuple[Tensor, Tensor]:
+    """GeneratorRRDB.forward, models.py:120-135 (default upsampling variant,
+    models.py:85-91; no final res blocks).  Returns (output, srs)."""
+    power = float(sd["power"].item())
+    multiplier = float(sd["multiplier"].item())
+    nb = _count(sd, "res_blocks.%d.")
+    up_idx = sorted({int(k.split(".")[1]) for k in sd if k.startswith("upsampling.") and k.endswith("weight")})
+
+    x = multiplier * (x ** power)                                            # models.py:122
+    out1 = F.conv2d(x, sd["conv1.weight"], sd["conv1.bias"], 1, 1)           # 123
+    out = out1
+    for i in range(nb):                                                      # 124
+        out = rrdb(sd, f"res_blocks.{i}.", out, res_scale)
+    out2 = F.conv2d(out, sd["conv2.weight"], sd["conv2.bias"], 1, 1)         # 125
+    out = out1 + out2                                                        # 126
+    for i in up_idx:                                                         # 127 / 85-91
+        out = F.conv2d(out, sd[f"upsampling.{i}.weight"], sd[f"upsampling.{i}.bias"], 1, 1)
+        out = F.leaky_relu(out, G_LRELU_SLOPE)
+        out = F.pixel_shuffle(out, 2)
+    out = F.conv2d(out, sd["conv3.0.weight"], sd["conv3.0.bias"], 1, 1)      # 131 / 96-100
+    out = F.leaky_relu(out, G_LRELU_SLOPE)
+    out = F.conv2d(out, sd["conv3.2.weight"], sd["conv3.2.bias"], 1, 1) / multiplier
+
+    def head(t: Tensor, p: float) -> Tensor:                                 # models.py:114-118
+        lambd = float(thres) ** p
+        if training:
+            return F.hardshrink(t, lambd)
+        return F.hardshrink(F.relu(t), lambd)
+
+    srs = head(out, power)                                                   # 132
+    if power != 1:                                                           # 133-134
+        out = F.relu(out) ** (1.0 / power)
+    return head(out, 1.0), srs                                               # 135
+
+
+# ----------------------------------------------------------------------------
+# discriminator (models.py:140-174) and SumPool2d (models.py:297-305)
+# ----------------------------------------------------------------------------
+def discriminator_forward(sd: SD, img: Tensor) -> Tensor:
+    """Markovian_Discriminator.forward, models.py:149-174: per channel entry
+    [conv s1, LReLU .2, conv s2, LReLU .2], then conv -> 1."""
+    idx = sorted({int(k.split(".")[1]) for k in sd if k.startswith("model.") and k.endswith("weight")})
+    out = img
+    for n, i in enumerate(idx):
+        last = n == len(idx) - 1
+        stride = 1 if (last or n % 2 == 0) else 2
+        out = F.conv2d(out, sd[f"model.{i}.weight"], sd[f"model.{i}.bias"], stride, 1)
+        if not last:
+            out = F.leaky_relu(out, D_LRELU_SLOPE)
+    return out
+
+
+def sum_pool(x: Tensor, k: int) -> Tensor:
+    """SumPool2d.forward, models.py:304-305: k*k*AvgPool2d(k)."""
+    return (k * k) * F.avg_pool2d(x, k)
+
+
+# ----------------------------------------------------------------------------
+# losses (esrgan.py:457-626), default-active terms only
+# ----------------------------------------------------------------------------
+EPS = 1e-7  # esrgan.py:319
+
+
+def bce_logits(x: Tensor, target_value: float) -> Tensor:
+    """nn.BCEWithLogitsLoss (mean) against a constant target, esrgan.py:244."""
+    t = torch.full_like(x, target_value)
+    return F.binary_cross_entropy_with_logits(x, t)
+
+
+def ragan_loss_g(pred_real: Tensor, pred_fake: Tensor) -> Tensor:
+    """esrgan.py:507-508."""
+    return 0.5 * (bce_logits(EPS + pred_fake - pred_real.mean(0, keepdim=True), 1.0)
+                  + bce_logits(EPS + pred_real - pred_fake.mean(0, keepdim=True), 0.0))
+
+
+def ragan_loss_d(pred_real: Tensor, pred_fake: Tensor) -> Tensor:
+    """esrgan.py:578-579,588."""
+    loss_real = bce_logits(EPS + pred_real - pred_fake.mean(0, keepdim=True), 1.0)
+    loss_fake = bce_logits(EPS + pred_fake - pred_real.mean(0, keepdim=True), 0.0)
+    return (loss_real + loss_fake) / 2
+
+
+def generator_loss(gen: Sequence[Tensor], hr: Tensor, lr: Tensor, d_sds: Sequence[SD], *, factor: int,
+                   scaling_power: float = 1.0, lambdas=(0.2, 1.0), lambda_hr=1.0, lambda_lr=0.1,
+                   lambda_adv=0.01) -> Tuple[Tensor, Dict[str, Tensor]]:
+    """G-step loss assembly, esrgan.py:468-552 with the default.json weights.
+    ``gen`` = (generator output, generator.srs)."""
+    ground_truth = (hr, hr ** scaling_power)                                  # 470
+    gen_lr = sum_pool(gen[0], factor)                                         # 471
+    generated_lr = (gen_lr, gen_lr ** scaling_power)                          # 472
+    ground_truth_lr = (lr, lr ** scaling_power)                               # 473
+    parts: Dict[str, Tensor] = {}
+    loss_g = torch.zeros(1)
+    for k in range(2):
+        if lambdas[k] <= 0:
+            continue
+        l_hr = F.l1_loss(gen[k].mean(0)[None], ground_truth[k].mean(0)[None])  # 487
+        l_lr = F.l1_loss(generated_lr[k], ground_truth_lr[k])                   # 490
+        pred_real = discriminator_forward(d_sds[k], ground_truth[k]).detach()   # 493
+        pred_fake = discriminator_forward(d_sds[k], gen[k])                     # 494
+        l_adv = ragan_loss_g(pred_real, pred_fake)                              # 507
+        tot = lambda_hr * l_hr + lambda_adv * l_adv + lambda_lr * l_lr          # 549
+        loss_g = loss_g + lambdas[k] * tot                                      # 552
+        parts[f"hr{k}"], parts[f"lr{k}"], parts[f"adv{k}"] = l_hr, l_lr, l_adv
+    return loss_g, parts
+
+
+def discriminator_loss(d_sd: SD, real: Tensor, fake: Tensor, epsilon: Tensor, *, lambda_reg=0.01
+                       ) -> Tuple[Tensor, Dict[str, Tensor]]:
+    """D-step loss for one discriminator, esrgan.py:569-606 (relativistic, with
+    gradient penalty).  ``epsilon`` is the (B,1,1,1) uniform draw of line 598."""
+    pred_real = discriminator_forward(d_sd, real)                              # 569
+    pred_fake = discriminator_forward(d_sd, fake.detach())                     # 570
+    loss = ragan_loss_d(pred_real, pred_fake)                                  # 578-588
+    parts = {"ragan": loss}
+    if lambda_reg > 0:
+        interp = (epsilon * real + (1 - epsilon) * fake.detach()).requires_grad_(True)   # 599-600
+        pred_i = discriminator_forward(d_sd, interp)                           # 601
+        grads = torch.autograd.grad(pred_i, interp, torch.ones_like(pred_i), create_graph=True)[0]  # 602
+        grads = grads.view(grads.shape[0], -1)                                 # 604
+        gp = ((grads.norm(2, dim=1) - 1) ** 2).mean() * lambda_reg / 2         # 605
+        loss = loss + gp                                                       # 606
+        parts["gp"] = gp
+    return loss, parts
+
+
+# ----------------------------------------------------------------------------
+# Adam (torch.optim.Adam as used at esrgan.py:299,305)
+# ----------------------------------------------------------------------------
+def adam_step(p: Tensor, g: Tensor, m: Tensor, v: Tensor, step: int, *, lr=2e-4, b1=0.9, b2=0.999,
+              eps=1e-8, weight_decay=0.0) -> None:
+    """One in-place Adam update with coupled L2 decay, no amsgrad; ``step`` is
+    the 1-based step count after increment."""
+    if weight_decay != 0:
+        g = g + weight_decay * p
+    m.mul_(b1).add_(g, alpha=1 - b1)
+    v.mul_(b2).addcmul_(g, g, value=1 - b2)
+    bc1 = 1 - b1 ** step
+    bc2 = 1 - b2 ** step
+    denom = (v.sqrt() / math.sqrt(bc2)).add_(eps)
+    p.addcdiv_(m, denom, value=-lr / bc1)
+
+
+# ----------------------------------------------------------------------------
+# synthetic sparse jet images and deterministic weights
+# ----------------------------------------------------------------------------
+def synthetic_jets(batch: int, hr: int, factor: int, seed: int) -> Tuple[Tensor, Tensor]:
+    """HR (B,1,hr,hr) with 20..60 non-zero pixels ~ Exp(mean 5), LR = SumPool(factor)(HR)
+    as datasets.py:247 does."""
+    g = torch.Generator().manual_seed(seed)
+    img = torch.zeros(batch, 1, hr, hr)
+    for b in range(batch):
+        n = int(torch.randint(20, 61, (1,), generator=g))
+        idx = torch.randperm(hr * hr, generator=g)[:n]
+        e = -5.0 * torch.log(1 - torch.rand(n, generator=g))
+        img[b, 0].view(-1)[idx] = e
+    return img, sum_pool(img, factor)
+
+
+def seeded_state_dict(shapes: Dict[str, Tuple[int, ...]], seed: int, gain: float = 1.0) -> SD:
+    """Deterministic weights: each tensor ~ U(-a, a), a = gain/sqrt(fan_in) (the
+    scale of nn.Conv2d's default init), from its own seeded generator, so the
+    same dict can be rebuilt anywhere without the reference."""
+    sd: SD = {}
+    for i, (name, shape) in enumerate(shapes.items()):
+        g = torch.Generator().manual_seed(seed * 100003 + i)
+        if name in ("power", "multiplier"):
+            continue
+        fan_in = int(np.prod(shape[1:])) if len(shape) > 1 else None
+        if fan_in is None:
+            # bias: use the weight's fan_in (previous entry)
+            prev = list(shapes.values())[i - 1]
+            fan_in = int(np.prod(prev[1:]))
+        a = gain / math.sqrt(fan_in)
+        sd[name] = (torch.rand(shape, generator=g) * 2 - 1) * a
+    return sd
+
+
+def generator_shapes(channels=1, filters=64, num_res_blocks=10, num_upsample=2) -> Dict[str, Tuple[int, ...]]:
+    """state_dict names/shapes of GeneratorRRDB in registration order (models.py:58-103;
+    SURVEY.md section 5 'Checkpoint')."""
+    s: Dict[str, Tuple[int, ...]] = {"power": (1,), "multiplier": (1,)}
+    F_ = filters
+    s["conv1.weight"] = (F_, channels, 3, 3); s["conv1.bias"] = (F_,)
+    for i in range(num_res_blocks):
+        for j in range(3):
+            for k in range(1, 6):
+                p = f"res_blocks.{i}.dense_blocks.{j}.b{k}.0."
+                s[p + "weight"] = (F_, k * F_, 3, 3); s[p + "bias"] = (F_,)
+    s["conv2.weight"] = (F_, F_, 3, 3); s["conv2.bias"] = (F_,)
+    for u in range(num_upsample):
+        s[f"upsampling.{3 * u}.weight"] = (4 * F_, F_, 3, 3); s[f"upsampling.{3 * u}.bias"] = (4 * F_,)
+    s["conv3.0.weight"] = (F_, F_, 3, 3); s["conv3.0.bias"] = (F_,)
+    s["conv3.2.weight"] = (channels, F_, 3, 3); s["conv3.2.bias"] = (channels,)
+    return s
+
+
+def discriminator_shapes(in_channels=1, channels=(16, 32, 32, 64)) -> Dict[str, Tuple[int, ...]]:
+    """state_dict names/shapes of Markovian_Discriminator (models.py:149-174)."""
+    s: Dict[str, Tuple[int, ...]] = {}
+    cin, idx = in_channels, 0
+    for c in channels:
+        s[f"model.{idx}.weight"] = (c, cin, 3, 3); s[f"model.{idx}.bias"] = (c,)
+        s[f"model.{idx + 2}.weight"] = (c, c, 3, 3); s[f"model.{idx + 2}.bias"] = (c,)
+        cin, idx = c, idx + 4
+    s[f"model.{idx}.weight"] = (1, cin, 3, 3); s[f"model.{idx}.bias"] = (1,)
+    return s
+
+
+def make_generator_sd(seed: int, *, channels=1, filters=64, num_res_blocks=10, num_upsample=2,
+                      power=1.0, multiplier=1.0, gain=1.0) -> SD:
+    shapes = generator_shapes(channels, filters, num_res_blocks, num_upsample)
+    sd = {"power": torch.tensor([float(power)]), "multiplier": torch.tensor([float(multiplier)])}
+    sd.update(seeded_state_dict(shapes, seed, gain))
+    return {k: sd[k] for k in shapes}
+
+
+def make_discriminator_sd(seed: int, *, in_channels=1, channels=(16, 32, 32, 64), gain=1.0) -> SD:
+    return seeded_state_dict(discriminator_shapes(in_channels, channels), seed, gain)
