@@ -1,0 +1,117 @@
+/* libsrb200 -- C ABI of the B200-native ESRGAN hot path.
+ *
+ * The reference (lukas-blecher/super-resolution) is pure Python and reaches its
+ * numeric backend through torch.nn calls; this library is what replaces that
+ * backend for the hot path.  Each entry point names the reference call site(s)
+ * it stands in for.  All entry points:
+ *   - are extern "C", take plain pointers / ints / floats (no torch types);
+ *   - take DEVICE pointers owned by the caller (the library never allocates or
+ *     frees device memory) and an explicit cudaStream_t passed as void*;
+ *   - are asynchronous, re-entrant and CUDA-graph capturable; they never call
+ *     cudaDeviceSynchronize;
+ *   - return 0 on success, non-zero on error; srb_last_error() then returns a
+ *     thread-local message that starts with "CUDA" (the Python shim raises
+ *     RuntimeError with that text, which the reference's handlers at
+ *     esrgan.py:829-836 and hyper_search.py:108-110 key on).
+ *
+ * Activation layout ("PNHWC"): bf16 [batch][H+1][W+1][C]; row H and column W
+ * of every image are zero.  With that padding a 3x3/pad-1 convolution is nine
+ * constant row-shifts of the flat [batch*(H+1)*(W+1), C] matrix, which is what
+ * the implicit-GEMM kernels exploit.  Kernels only ever store to valid pixels,
+ * so a buffer zero-filled once at allocation keeps its padding forever.
+ */
+#ifndef SRB200_H
+#define SRB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SRB_ABI_VERSION 1
+
+const char* srb_last_error(void);
+int srb_abi_version(void);
+/* Reads and clears the device-side fault word (non-zero after a kernel trapped on a pipeline wait). */
+int srb_read_fault(unsigned int* fault_out);
+
+/* ---- 3x3 stride-1 pad-1 convolution, channels multiple of 64, PNHWC bf16 ----------------------
+ * Replaces: nn.Conv2d in DenseResidualBlock b1..b5 (models.py:19,36-38) incl. torch.cat (38) and
+ * out.mul(res_scale)+x (41,53); conv2 + torch.add (models.py:67,125-126); upsampling conv +
+ * LeakyReLU + PixelShuffle (models.py:87-89); conv3.0 + LeakyReLU (models.py:97-98); and, with the
+ * "dgrad" weight pack, the input-gradient of all of those (aten::convolution_backward).
+ *
+ *   v = (acc + bias) * alpha + res1 * res1_scale + res2 * res2_scale
+ *   act == SRB_ACT_LRELU      : v = v > 0 ? v : slope * v
+ *   act == SRB_ACT_LRELU_MASK : v = v * (mask > 0 ? 1 : slope)          (LeakyReLU backward)
+ *   store_mode == SRB_STORE_PLAIN  : y[pixel][y_coff + n]
+ *   store_mode == SRB_STORE_SHUFFLE: cout = 4*Cy; packed output channel n = (2i+j)*Cy + c goes to
+ *                                    y[(2y+i, 2x+j)][y_coff + c]; y has geometry (2H, 2W).
+ */
+enum { SRB_ACT_NONE = 0, SRB_ACT_LRELU = 1, SRB_ACT_LRELU_MASK = 2 };
+enum { SRB_STORE_PLAIN = 0, SRB_STORE_SHUFFLE = 1 };
+enum { SRB_IMPL_TCGEN05 = 0, SRB_IMPL_NAIVE = 1 };
+
+typedef struct srb_conv3x3_args {
+  int batch, H, W;             /* un-padded geometry of x (and of y for SRB_STORE_PLAIN) */
+  const void* x;               /* bf16 PNHWC */
+  int x_cstride, x_coff, cin;  /* channels [x_coff, x_coff+cin) are read; cin % 64 == 0 */
+  const void* w;               /* bf16 packed [9][cin/64][cout][64]  (srb_pack_conv3x3_weights) */
+  const float* bias;           /* fp32 [cout] in packed channel order, or NULL */
+  int cout;                    /* % 64 == 0 */
+  void* y;                     /* bf16 PNHWC */
+  int y_cstride, y_coff;
+  int store_mode;
+  float alpha;
+  int act;
+  float slope;
+  const void* mask; int mask_cstride, mask_coff;
+  const void* res1; int res1_cstride, res1_coff; float res1_scale;
+  const void* res2; int res2_cstride, res2_coff; float res2_scale;
+  int impl;                    /* SRB_IMPL_* */
+  int flags;                   /* bit0: descriptor base-offset mode (bring-up switch) */
+} srb_conv3x3_args;
+
+int srb_conv3x3(const srb_conv3x3_args* a, void* stream);
+
+/* Weight packing, fp32 OIHW -> bf16 [9][cin/64][cout][64].
+ *   mode 0 (forward):  wp[t][kb][n][k] = w[perm(n)][kb*64+k][t] * scale
+ *   mode 1 (dgrad)  :  treats `w` as the forward weight [co][ci_total][3][3]; produces the pack of the
+ *                      transposed/flipped filter for input channels [ci_off, ci_off+64):
+ *                      wp[t][kb][n][k] = w[co_base... see DESIGN.md]
+ * shuffle != 0 permutes output channels n = (2i+j)*C + c <- 4c + 2i + j (PixelShuffle(2) order).
+ * Replaces nothing in the reference (layout glue); cites models.py:19 for the OIHW source layout. */
+int srb_pack_conv3x3_fwd(const float* w_oihw, int cout, int cin, int shuffle, float scale, void* wp, void* stream);
+/* dgrad pack of one forward conv restricted to input-channel slot [ci_off, ci_off+n_out) as OUTPUT channels:
+ *   wp[t][kb][n][k] = scale * w[kb_off_co + kb*64 + k][ci_off + n][8 - t]
+ * written at k-block offset kb_dst of a destination pack that has kb_total k-blocks (so several forward
+ * convs can be concatenated along K: the dense-block backward of SURVEY.md section 7-2). */
+int srb_pack_conv3x3_dgrad(const float* w_oihw, int cout, int cin, int ci_off, int n_out, int unshuffle,
+                           float scale, void* wp, int kb_dst, int kb_total, void* stream);
+
+/* ---- weight gradient of the same convolution -------------------------------------------------
+ * Replaces aten::convolution_backward (filter part) for every 64-multiple conv of the generator.
+ *   dw[co][ci][t] (+)= alpha * sum_pixels gy[p][co] * x[p + shift_t][ci];   dbias[co] (+)= alpha * sum gy
+ */
+typedef struct srb_wgrad3x3_args {
+  int batch, H, W;
+  const void* x;  int x_cstride, x_coff, cin;     /* bf16 PNHWC */
+  const void* gy; int gy_cstride, gy_coff, cout;  /* bf16 PNHWC, gradient of the pre-activation */
+  float* dw;       /* fp32 OIHW [cout][cin][3][3] */
+  float* dbias;    /* fp32 [cout] or NULL */
+  float alpha;
+  int accumulate;  /* 0: overwrite, 1: add into dw/dbias */
+  int unshuffle;   /* gy channel n = (2i+j)*C + c maps to dw row 4c+2i+j */
+  void* workspace; size_t workspace_bytes;
+  int impl;
+  int flags;
+} srb_wgrad3x3_args;
+int srb_wgrad3x3(const srb_wgrad3x3_args* a, void* stream);
+size_t srb_wgrad3x3_workspace_bytes(int batch, int H, int W, int cin, int cout);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRB200_H */

@@ -1,0 +1,353 @@
+// K1: 3x3 stride-1 pad-1 convolution as an implicit GEMM on tcgen05 tensor cores (sm_100a).
+//
+// Replaces the cuDNN/oneDNN convolutions behind models.py:19,36-41,53 (dense blocks incl. concat and
+// residual adds), models.py:67,125-126 (conv2 + skip), models.py:87-89 (upsampling conv + LeakyReLU +
+// PixelShuffle), models.py:97-98 (conv3.0 + LeakyReLU) and their input gradients.
+//
+// Formulation.  Activations are PNHWC bf16 (see include/srb200.h): the flat matrix X[R = B*(H+1)*(W+1), C]
+// has zero rows/columns between images, so tap (dy,dx) of the convolution is the constant row shift
+// s = dy*(W+1) + dx of X.  One CTA owns MT*128 consecutive flat rows (pixels) and one 64-wide slice of the
+// output channels:
+//   D[128*MT x 64] = sum over k-blocks kb (64 input channels) and taps t of  X[q0+s_t .. , kb] * Wp[t][kb]^T
+// A operand: ONE TMA load per k-block of the halo window rows [q0-halo, q0+128*MT+halo) x 64 channels into
+//   128B-swizzled shared memory; the nine taps are nine UMMA descriptors whose start address is offset by
+//   (halo + s_t) rows into that window (no re-load, no im2col).
+// B operand: per (k-block, tap) a 64x64 K-major weight tile (8 KB) streamed through a ring of slots.
+// Accumulators: MT x 64 fp32 columns of TMEM, double buffered so the epilogue of tile i overlaps the MMAs
+//   of tile i+1.  Persistent CTAs, static round-robin tile schedule.
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2..5 = epilogue
+//   (TMEM -> registers -> bias/scale/residual/activation -> bf16 global stores).
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace srb {
+
+constexpr int kIgemmThreads = 192;
+constexpr int kBSlots = 12;          // weight-tile ring (8 KB each)
+constexpr int kAStages = 2;          // halo-window ring
+constexpr int kBTileBytes = 64 * 64 * 2;
+
+struct IgemmParams {
+  int R;            // total flat rows = batch * P
+  int P, pitch, H, W;
+  int KB;           // cin / 64
+  int cout;
+  int n_ntiles;     // cout / 64
+  int num_work;     // n_mtiles * n_ntiles
+  int x_coff;
+  int halo;         // pitch + 1
+  int a_box_rows, a_nbox;   // TMA boxes per halo window
+  uint32_t a_stage_bytes;
+  const float* bias;
+  __nv_bfloat16* y; int y_cstride, y_coff;
+  int store_mode;   // SRB_STORE_*
+  int y_pitch, y_P; // geometry of y (== pitch,P for plain; 2W+1,(2H+1)(2W+1) for shuffle)
+  float alpha;
+  int act; float slope;
+  const __nv_bfloat16* mask; int mask_cstride, mask_coff;
+  const __nv_bfloat16* res1; int res1_cstride, res1_coff; float res1_scale;
+  const __nv_bfloat16* res2; int res2_cstride, res2_coff; float res2_scale;
+  int base_offset_mode;
+};
+
+__device__ __forceinline__ void load_row64(const __nv_bfloat16* p, uint4 (&v)[8]) {
+  const uint4* q = reinterpret_cast<const uint4*>(p);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __ldg(q + i);
+}
+
+template <int MT>
+__global__ void __launch_bounds__(kIgemmThreads, 1)
+conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                     const IgemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // carve: [A stages][B slots][barriers]
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* a_smem = smem;
+  uint8_t* b_smem = a_smem + kAStages * p.a_stage_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(b_smem + kBSlots * kBTileBytes);
+  uint64_t* a_full = bars;                      // [kAStages]
+  uint64_t* a_empty = a_full + kAStages;        // [kAStages]
+  uint64_t* b_full = a_empty + kAStages;        // [kBSlots]
+  uint64_t* b_empty = b_full + kBSlots;         // [kBSlots]
+  uint64_t* t_full = b_empty + kBSlots;         // [2]
+  uint64_t* t_empty = t_full + 2;               // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  constexpr uint32_t kTmemCols = 2 * 64 * MT;   // 128 or 256: power of two
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_w);
+    for (int i = 0; i < kAStages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
+    for (int i = 0; i < kBSlots; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 4); }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int rows_per_tile = 128 * MT;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
+      for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+        const int nt = work % p.n_ntiles;
+        const int mt_idx = work / p.n_ntiles;
+        const int q0 = mt_idx * rows_per_tile;
+        for (int kb = 0; kb < p.KB; ++kb) {
+          mbar_wait(&a_empty[sa], pa ^ 1, 1);
+          mbar_expect_tx(&a_full[sa], p.a_stage_bytes);
+          for (int bx = 0; bx < p.a_nbox; ++bx)
+            tma_load_2d(a_smem + sa * p.a_stage_bytes + bx * p.a_box_rows * 128, &tmap_x, p.x_coff + kb * 64,
+                        q0 - p.halo + bx * p.a_box_rows, &a_full[sa]);
+          if (++sa == kAStages) { sa = 0; pa ^= 1; }
+          for (int t = 0; t < 9; ++t) {
+            mbar_wait(&b_empty[sb], pb ^ 1, 2);
+            mbar_expect_tx(&b_full[sb], kBTileBytes);
+            tma_load_2d(b_smem + sb * kBTileBytes, &tmap_w, 0, (t * p.KB + kb) * p.cout + nt * 64, &b_full[sb]);
+            if (++sb == kBSlots) { sb = 0; pb ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc = make_idesc_bf16(128, 64, 0, 0);
+    uint32_t sa = 0, pa = 0, sb = 0, pb = 0, as = 0, pt = 0;
+    for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+      mbar_wait(&t_empty[as], pt ^ 1, 3);
+      tc_fence_after();
+      for (int kb = 0; kb < p.KB; ++kb) {
+        mbar_wait(&a_full[sa], pa, 4);
+        const uint32_t a_base = smem_u32(a_smem + sa * p.a_stage_bytes);
+        for (int t = 0; t < 9; ++t) {
+          mbar_wait(&b_full[sb], pb, 5);
+          tc_fence_after();
+          if (elect_one()) {
+            const int shift = p.halo + (t / 3 - 1) * p.pitch + (t % 3 - 1);
+            const uint32_t b_base = smem_u32(b_smem + sb * kBTileBytes);
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) {
+              const uint32_t a_tap = a_base + static_cast<uint32_t>(shift + mt * 128) * 128u;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint64_t ad = make_sw128_desc(a_tap + k * 32, 16, 1024, p.base_offset_mode);
+                const uint64_t bd = make_sw128_desc(b_base + k * 32, 16, 1024, 0);
+                umma_bf16(tmem_base + as * (64 * MT) + mt * 64, ad, bd, idesc, (kb | t | k) != 0);
+              }
+            }
+            umma_commit(&b_empty[sb]);
+            if (t == 8) umma_commit(&a_empty[sa]);
+            if (t == 8 && kb == p.KB - 1) umma_commit(&t_full[as]);
+          }
+          __syncwarp();
+          if (++sb == kBSlots) { sb = 0; pb ^= 1; }
+        }
+        if (++sa == kAStages) { sa = 0; pa ^= 1; }
+      }
+      if (++as == 2) { as = 0; pt ^= 1; }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps 2..5
+    const int lg = warp & 3;                    // TMEM lane group this warp may access
+    uint32_t as = 0, pt = 0;
+    for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+      const int nt = work % p.n_ntiles;
+      const int mt_idx = work / p.n_ntiles;
+      mbar_wait(&t_full[as], pt, 6);
+      tc_fence_after();
+#pragma unroll 1
+      for (int mt = 0; mt < MT; ++mt) {
+        const int q = mt_idx * rows_per_tile + mt * 128 + lg * 32 + lane;
+        const int r = q % p.P;
+        const int py = r / p.pitch, px = r - py * p.pitch;
+        const bool valid = (q < p.R) && (px < p.W) && (py < p.H);
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + as * (64 * MT) + mt * 64;
+        const int n0 = nt * 64;
+        // destination row
+        size_t yrow;
+        int ycoff = p.y_coff;
+        if (p.store_mode == SRB_STORE_SHUFFLE) {
+          const int img = q / p.P;
+          const int sub = nt & 3;               // (i,j) = (sub>>1, sub&1); Cy == 64
+          yrow = static_cast<size_t>(img) * p.y_P + static_cast<size_t>(2 * py + (sub >> 1)) * p.y_pitch +
+                 (2 * px + (sub & 1));
+          ycoff += (nt >> 2) * 64;
+        } else {
+          yrow = static_cast<size_t>(q);
+          ycoff += n0;
+        }
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t acc[32];
+          tmem_ld32(taddr + half * 32, acc);
+          tmem_ld_wait();
+          if (valid) {
+            const int c0 = n0 + half * 32;
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]);
+            if (p.bias) {
+              const float4* b4 = reinterpret_cast<const float4*>(p.bias + c0);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float4 b = __ldg(b4 + i);
+                v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] *= p.alpha;
+            if (p.res1) {
+              const uint4* rp = reinterpret_cast<const uint4*>(p.res1 + static_cast<size_t>(q) * p.res1_cstride +
+                                                               p.res1_coff + c0);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint4 u = __ldg(rp + i);
+                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  v[8 * i + 2 * j] += p.res1_scale * bf16lo(w[j]);
+                  v[8 * i + 2 * j + 1] += p.res1_scale * bf16hi(w[j]);
+                }
+              }
+            }
+            if (p.res2) {
+              const uint4* rp = reinterpret_cast<const uint4*>(p.res2 + static_cast<size_t>(q) * p.res2_cstride +
+                                                               p.res2_coff + c0);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint4 u = __ldg(rp + i);
+                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  v[8 * i + 2 * j] += p.res2_scale * bf16lo(w[j]);
+                  v[8 * i + 2 * j + 1] += p.res2_scale * bf16hi(w[j]);
+                }
+              }
+            }
+            if (p.act == SRB_ACT_LRELU) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.slope;
+            } else if (p.act == SRB_ACT_LRELU_MASK) {
+              const uint4* mp = reinterpret_cast<const uint4*>(p.mask + static_cast<size_t>(q) * p.mask_cstride +
+                                                               p.mask_coff + c0);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint4 u = __ldg(mp + i);
+                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  v[8 * i + 2 * j] *= bf16lo(w[j]) > 0.f ? 1.f : p.slope;
+                  v[8 * i + 2 * j + 1] *= bf16hi(w[j]) > 0.f ? 1.f : p.slope;
+                }
+              }
+            }
+            uint4* yp = reinterpret_cast<uint4*>(p.y + yrow * p.y_cstride + ycoff + half * 32);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              uint4 o;
+              o.x = pack_bf16(v[8 * i], v[8 * i + 1]);
+              o.y = pack_bf16(v[8 * i + 2], v[8 * i + 3]);
+              o.z = pack_bf16(v[8 * i + 4], v[8 * i + 5]);
+              o.w = pack_bf16(v[8 * i + 6], v[8 * i + 7]);
+              yp[i] = o;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&t_empty[as]);
+      if (++as == 2) { as = 0; pt ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------------- host side
+static size_t igemm_smem_bytes(uint32_t a_stage_bytes) {
+  return 1024 + size_t(kAStages) * a_stage_bytes + size_t(kBSlots) * kBTileBytes + 512;
+}
+
+int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
+  if (a->cin % 64 || a->cout % 64 || a->cin <= 0 || a->cout <= 0) return set_error("conv3x3: channels must be multiples of 64");
+  if ((a->x_cstride % 8) || (a->y_cstride % 8) || (a->x_coff % 64) || (a->y_coff % 8))
+    return set_error("conv3x3: channel strides/offsets must keep 16-byte alignment");
+  if (a->store_mode == SRB_STORE_SHUFFLE && a->cout != 256) return set_error("conv3x3: shuffle store needs cout == 256");
+  const int pitch = a->W + 1, P = (a->H + 1) * (a->W + 1);
+  const long long R = 1LL * a->batch * P;
+  if (R <= 0 || R > 0x7fffffffLL) return set_error("conv3x3: bad geometry");
+  const int halo = pitch + 1;
+
+  // tile height: two 128-row sub-tiles per CTA when that still fills the machine
+  const int sms = sm_count();
+  const int n_ntiles = a->cout / 64;
+  int MT = 2;
+  if (((R + 255) / 256) * n_ntiles < sms) MT = 1;
+  int rows_tile = 128 * MT;
+  int win = rows_tile + 2 * halo;
+  int win8 = (win + 7) & ~7;
+  int nbox = (win8 + 255) / 256;
+  int box_rows = (((win8 + nbox - 1) / nbox) + 7) & ~7;
+  uint32_t a_stage_bytes = uint32_t(nbox) * box_rows * 128;
+  size_t smem = igemm_smem_bytes(a_stage_bytes);
+  if (smem > 227 * 1024 && MT == 2) {
+    MT = 1; rows_tile = 128; win = rows_tile + 2 * halo; win8 = (win + 7) & ~7;
+    nbox = (win8 + 255) / 256; box_rows = (((win8 + nbox - 1) / nbox) + 7) & ~7;
+    a_stage_bytes = uint32_t(nbox) * box_rows * 128; smem = igemm_smem_bytes(a_stage_bytes);
+  }
+  if (smem > 227 * 1024) return set_error("conv3x3: image too wide for the tcgen05 kernel (W <= ~400)");
+
+  CUtensorMap tx, tw;
+  if (make_tmap_2d_bf16(&tx, a->x, (uint64_t)a->x_cstride, (uint64_t)R, (uint64_t)a->x_cstride * 2, 64, box_rows))
+    return 1;
+  if (make_tmap_2d_bf16(&tw, a->w, 64, (uint64_t)9 * (a->cin / 64) * a->cout, 128, 64, 64)) return 1;
+
+  IgemmParams p{};
+  p.R = (int)R; p.P = P; p.pitch = pitch; p.H = a->H; p.W = a->W;
+  p.KB = a->cin / 64; p.cout = a->cout; p.n_ntiles = n_ntiles;
+  const int n_mtiles = int((R + rows_tile - 1) / rows_tile);
+  p.num_work = n_mtiles * n_ntiles;
+  p.x_coff = a->x_coff; p.halo = halo; p.a_box_rows = box_rows; p.a_nbox = nbox; p.a_stage_bytes = a_stage_bytes;
+  p.bias = a->bias;
+  p.y = (__nv_bfloat16*)a->y; p.y_cstride = a->y_cstride; p.y_coff = a->y_coff; p.store_mode = a->store_mode;
+  if (a->store_mode == SRB_STORE_SHUFFLE) { p.y_pitch = 2 * a->W + 1; p.y_P = (2 * a->H + 1) * (2 * a->W + 1); }
+  else { p.y_pitch = pitch; p.y_P = P; }
+  p.alpha = a->alpha; p.act = a->act; p.slope = a->slope;
+  p.mask = (const __nv_bfloat16*)a->mask; p.mask_cstride = a->mask_cstride; p.mask_coff = a->mask_coff;
+  p.res1 = (const __nv_bfloat16*)a->res1; p.res1_cstride = a->res1_cstride; p.res1_coff = a->res1_coff; p.res1_scale = a->res1_scale;
+  p.res2 = (const __nv_bfloat16*)a->res2; p.res2_cstride = a->res2_cstride; p.res2_coff = a->res2_coff; p.res2_scale = a->res2_scale;
+  p.base_offset_mode = a->flags & 1;
+  if (p.act == SRB_ACT_LRELU_MASK && !p.mask) return set_error("conv3x3: mask activation without mask tensor");
+
+  const int grid = p.num_work < sms ? p.num_work : sms;
+  cudaError_t e;
+  if (MT == 2) {
+    static bool attr2 = false;
+    if (!attr2) { cudaFuncSetAttribute(conv3x3_igemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr2 = true; }
+    conv3x3_igemm_kernel<2><<<grid, kIgemmThreads, smem, stream>>>(tx, tw, p);
+  } else {
+    static bool attr1 = false;
+    if (!attr1) { cudaFuncSetAttribute(conv3x3_igemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr1 = true; }
+    conv3x3_igemm_kernel<1><<<grid, kIgemmThreads, smem, stream>>>(tx, tw, p);
+  }
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error("conv3x3_igemm launch", e);
+  return 0;
+}
+
+}  // namespace srb

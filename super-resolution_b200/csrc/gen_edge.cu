@@ -1,0 +1,370 @@
+// K4: the bandwidth-bound ends of the generator.
+//   conv_in : models.py:122-123  x -> multiplier * x**power -> conv1 (channels -> F), fp32 NCHW image in,
+//             PNHWC bf16 out (written into slot 0 of the first dense block's growth buffer).
+//   conv_out: models.py:99,131-135 + out() 114-118: conv3.2 (F -> channels) / multiplier, then the output head
+//             (hardshrink / relu / **(1/power)); writes the image `out`, the side output `srs` and the
+//             pre-head value z (kept for backward).
+//   Their backward kernels, and the PixelShuffle adjoint ("unshuffle") used by the upsampling backward.
+// All are CUDA-core kernels: K = 9*channels or N = channels (1 by default) cannot feed a tensor core.
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace srb {
+
+// ---------------------------------------------------------------- conv_in forward
+// one thread = one pixel x 8 output channels (16-byte store)
+__global__ void conv_in_fwd_kernel(const float* __restrict__ img, int B, int Cimg, int H, int W, float multiplier,
+                                   float power, const float* __restrict__ w, const float* __restrict__ bias, int F,
+                                   __nv_bfloat16* __restrict__ y, int y_cstride, int y_coff,
+                                   __nv_bfloat16* __restrict__ y2, int y2_cstride, int y2_coff) {
+  const int groups = F / 8;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long total = 1LL * B * H * W * groups;
+  if (idx >= total) return;
+  const int g = int(idx % groups);
+  long long r = idx / groups;
+  const int px = int(r % W); r /= W;
+  const int py = int(r % H);
+  const int b = int(r / H);
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = bias[g * 8 + i];
+  for (int c = 0; c < Cimg; ++c) {
+    const float* ip = img + (static_cast<size_t>(b) * Cimg + c) * H * W;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const int yy = py + t / 3 - 1, xx = px + t % 3 - 1;
+      if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+      float v = ip[yy * W + xx];
+      if (power != 1.f) v = powf(v, power);
+      v *= multiplier;
+      if (v == 0.f) continue;                                   // jet images are >99% zeros
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] += v * __ldg(w + (static_cast<size_t>(g * 8 + i) * Cimg + c) * 9 + t);
+    }
+  }
+  uint4 o;
+  o.x = pack_bf16(acc[0], acc[1]); o.y = pack_bf16(acc[2], acc[3]);
+  o.z = pack_bf16(acc[4], acc[5]); o.w = pack_bf16(acc[6], acc[7]);
+  const size_t row = (static_cast<size_t>(b) * (H + 1) + py) * (W + 1) + px;
+  *reinterpret_cast<uint4*>(y + row * y_cstride + y_coff + g * 8) = o;
+  if (y2) *reinterpret_cast<uint4*>(y2 + row * y2_cstride + y2_coff + g * 8) = o;
+}
+
+// ---------------------------------------------------------------- conv_in backward (weights only)
+// dW[f][c][t] += sum_p g[p][f] * xin[p + s_t][c];  db[f] += sum_p g[p][f].   grid.x = pixel chunks;
+// block = 256 threads = F(64) x 4 pixel lanes (F <= 64 per blockIdx.y slice).
+__global__ void conv_in_bwd_kernel(const float* __restrict__ img, int B, int Cimg, int H, int W, float multiplier,
+                                   float power, const __nv_bfloat16* __restrict__ g, int g_cstride, int g_coff, int F,
+                                   float* __restrict__ dw, float* __restrict__ db, int pix_per_block) {
+  const int f = blockIdx.y * 64 + (threadIdx.x & 63);
+  const int pl = threadIdx.x >> 6;
+  const long long npix = 1LL * B * H * W;
+  const long long p0 = 1LL * blockIdx.x * pix_per_block;
+  long long p1 = p0 + pix_per_block; if (p1 > npix) p1 = npix;
+  float acc[9 * 4];   // up to 4 image channels
+#pragma unroll
+  for (int i = 0; i < 36; ++i) acc[i] = 0.f;
+  float bsum = 0.f;
+  const int Cc = Cimg < 4 ? Cimg : 4;
+  for (long long pidx = p0 + pl; pidx < p1; pidx += 4) {
+    const int px = int(pidx % W); const int py = int((pidx / W) % H); const int b = int(pidx / (1LL * W * H));
+    const size_t row = (static_cast<size_t>(b) * (H + 1) + py) * (W + 1) + px;
+    const float gv = f < F ? __bfloat162float(g[row * g_cstride + g_coff + f]) : 0.f;
+    bsum += gv;
+    if (gv == 0.f) continue;
+    for (int c = 0; c < Cc; ++c) {
+      const float* ip = img + (static_cast<size_t>(b) * Cimg + c) * H * W;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const int yy = py + t / 3 - 1, xx = px + t % 3 - 1;
+        if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+        float v = ip[yy * W + xx];
+        if (power != 1.f) v = powf(v, power);
+        acc[c * 9 + t] += gv * v * multiplier;
+      }
+    }
+  }
+  __shared__ float red[4][64][37];
+#pragma unroll
+  for (int i = 0; i < 36; ++i) red[pl][threadIdx.x & 63][i] = acc[i];
+  red[pl][threadIdx.x & 63][36] = bsum;
+  __syncthreads();
+  if (pl == 0 && f < F) {
+    for (int i = 0; i < Cc * 9; ++i) {
+      const float s = red[0][threadIdx.x][i] + red[1][threadIdx.x][i] + red[2][threadIdx.x][i] + red[3][threadIdx.x][i];
+      if (s != 0.f) atomicAdd(dw + (static_cast<size_t>(f) * Cimg + i / 9) * 9 + i % 9, s);
+    }
+    const float s = red[0][threadIdx.x][36] + red[1][threadIdx.x][36] + red[2][threadIdx.x][36] + red[3][threadIdx.x][36];
+    atomicAdd(db + f, s);
+  }
+}
+
+// ---------------------------------------------------------------- conv_out forward + head
+__device__ __forceinline__ float hardshrink(float v, float l) { return (v > l || v < -l) ? v : 0.f; }
+
+// one warp = one output pixel (all image channels, normally 1); lane = channel pair of the 64-wide input
+__global__ void conv_out_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_cstride, int x_coff, int B, int H, int W,
+                                    int F, const float* __restrict__ w, const float* __restrict__ bias, int Cimg,
+                                    float inv_multiplier, float power, float thres, int training,
+                                    float* __restrict__ out, float* __restrict__ srs, float* __restrict__ z) {
+  const int lane = threadIdx.x & 31;
+  const long long wid = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long npix = 1LL * B * H * W;
+  if (wid >= npix) return;
+  const int px = int(wid % W); const int py = int((wid / W) % H); const int b = int(wid / (1LL * W * H));
+  const int pitch = W + 1;
+  const long long row = (static_cast<long long>(b) * (H + 1) + py) * pitch + px;
+  const long long R = 1LL * B * (H + 1) * pitch;
+  for (int oc = 0; oc < Cimg; ++oc) {
+    float acc = 0.f;
+    for (int c0 = lane * 2; c0 < F; c0 += 64) {
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const long long rs = row + (t / 3 - 1) * pitch + (t % 3 - 1);
+        if (rs < 0 || rs >= R) continue;
+        const uint32_t v = *reinterpret_cast<const uint32_t*>(x + rs * x_cstride + x_coff + c0);
+        acc += bf16lo(v) * __ldg(w + (static_cast<size_t>(oc) * F + c0) * 9 + t) +
+               bf16hi(v) * __ldg(w + (static_cast<size_t>(oc) * F + c0 + 1) * 9 + t);
+      }
+    }
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+      const float zz = (acc + bias[oc]) * inv_multiplier;
+      const size_t oi = ((static_cast<size_t>(b) * Cimg + oc) * H + py) * W + px;
+      if (z) z[oi] = zz;
+      // models.py:132  srs = out(z, power): hardshrink(z or relu(z), thres**power)
+      const float lam_p = powf(thres, power);
+      float s = training ? zz : fmaxf(zz, 0.f);
+      srs[oi] = hardshrink(s, lam_p);
+      float o2 = zz;
+      if (power != 1.f) o2 = powf(fmaxf(zz, 0.f), 1.f / power);      // models.py:133-134
+      if (!training) o2 = fmaxf(o2, 0.f);
+      out[oi] = hardshrink(o2, thres);                               // models.py:135
+    }
+  }
+}
+
+// gz[b][c][y][x] = g_out * d out/dz + g_srs * d srs/dz   (training-mode head, models.py:114-116,131-135)
+__global__ void head_bwd_kernel(const float* __restrict__ z, const float* __restrict__ g_out,
+                                const float* __restrict__ g_srs, long long n, float inv_multiplier, float power,
+                                float thres, int training, float* __restrict__ gz) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float zz = z[i];
+  float g = 0.f;
+  if (g_srs) {
+    const float lam_p = powf(thres, power);
+    const float s = training ? zz : fmaxf(zz, 0.f);
+    const bool pass = (s > lam_p || s < -lam_p) && (training || zz > 0.f);
+    if (pass) g += g_srs[i];
+  }
+  if (g_out) {
+    float o2 = zz, d = 1.f;
+    if (power != 1.f) {
+      if (zz > 0.f) { o2 = powf(zz, 1.f / power); d = o2 / (power * zz); } else { o2 = 0.f; d = 0.f; }
+    }
+    if (!training && o2 <= 0.f) d = 0.f;
+    if (o2 > thres || o2 < -thres) g += g_out[i] * d;
+  }
+  gz[i] = g * inv_multiplier;     // z = conv / multiplier
+}
+
+// conv_out input gradient: gy[p][c] = (sum_t w[oc][c][t] * gz[p - s_t]) * lrelu'(act[p][c]); PNHWC bf16 out.
+// one thread = one pixel x 8 channels
+__global__ void conv_out_dgrad_kernel(const float* __restrict__ gz, int B, int Cimg, int H, int W,
+                                      const float* __restrict__ w, int F, const __nv_bfloat16* __restrict__ act,
+                                      int act_cstride, int act_coff, float slope, __nv_bfloat16* __restrict__ gy,
+                                      int gy_cstride, int gy_coff) {
+  const int groups = F / 8;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long total = 1LL * B * H * W * groups;
+  if (idx >= total) return;
+  const int g = int(idx % groups);
+  long long r = idx / groups;
+  const int px = int(r % W); r /= W;
+  const int py = int(r % H);
+  const int b = int(r / H);
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  for (int oc = 0; oc < Cimg; ++oc) {
+    const float* gp = gz + (static_cast<size_t>(b) * Cimg + oc) * H * W;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const int yy = py - (t / 3 - 1), xx = px - (t % 3 - 1);
+      if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+      const float v = gp[yy * W + xx];
+      if (v == 0.f) continue;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] += v * __ldg(w + (static_cast<size_t>(oc) * F + g * 8 + i) * 9 + t);
+    }
+  }
+  const size_t row = (static_cast<size_t>(b) * (H + 1) + py) * (W + 1) + px;
+  const uint4 a = *reinterpret_cast<const uint4*>(act + row * act_cstride + act_coff + g * 8);
+  const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+  uint32_t ow[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float m0 = bf16lo(aw[j]) > 0.f ? 1.f : slope, m1 = bf16hi(aw[j]) > 0.f ? 1.f : slope;
+    ow[j] = pack_bf16(acc[2 * j] * m0, acc[2 * j + 1] * m1);
+  }
+  *reinterpret_cast<uint4*>(gy + row * gy_cstride + gy_coff + g * 8) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+}
+
+// conv_out weight gradient: dw[oc][c][t] += sum_p gz[p] * act[p + s_t][c]; db[oc] += sum gz.
+// block = 256 threads: lane pair-of-channels (32) x 8 pixel lanes; each block reduces a pixel chunk.
+__global__ void conv_out_wgrad_kernel(const float* __restrict__ gz, int B, int Cimg, int H, int W,
+                                      const __nv_bfloat16* __restrict__ act, int act_cstride, int act_coff, int F,
+                                      float* __restrict__ dw, float* __restrict__ db, int pix_per_block) {
+  const int cp = threadIdx.x & 31, pl = threadIdx.x >> 5;
+  const int c0 = blockIdx.y * 64 + cp * 2;
+  const long long npix = 1LL * B * H * W;
+  const long long p0 = 1LL * blockIdx.x * pix_per_block;
+  long long p1 = p0 + pix_per_block; if (p1 > npix) p1 = npix;
+  const int pitch = W + 1;
+  const long long R = 1LL * B * (H + 1) * pitch;
+  for (int oc = 0; oc < Cimg; ++oc) {
+    float a0[9], a1[9], bs = 0.f;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) { a0[t] = 0.f; a1[t] = 0.f; }
+    for (long long pidx = p0 + pl; pidx < p1; pidx += 8) {
+      const int px = int(pidx % W); const int py = int((pidx / W) % H); const int b = int(pidx / (1LL * W * H));
+      const float gv = gz[((static_cast<size_t>(b) * Cimg + oc) * H + py) * W + px];
+      if (gv == 0.f) continue;
+      bs += gv;
+      const long long row = (static_cast<long long>(b) * (H + 1) + py) * pitch + px;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const long long rs = row + (t / 3 - 1) * pitch + (t % 3 - 1);
+        if (rs < 0 || rs >= R) continue;
+        const uint32_t v = *reinterpret_cast<const uint32_t*>(act + rs * act_cstride + act_coff + c0);
+        a0[t] += gv * bf16lo(v); a1[t] += gv * bf16hi(v);
+      }
+    }
+    __shared__ float red[8][64][9];
+    __shared__ float redb[8];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) { red[pl][cp * 2][t] = a0[t]; red[pl][cp * 2 + 1][t] = a1[t]; }
+    if (cp == 0) redb[pl] = bs;
+    __syncthreads();
+    for (int i = threadIdx.x; i < 64 * 9; i += blockDim.x) {
+      const int c = i / 9, t = i % 9;
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s += red[k][c][t];
+      if (s != 0.f && blockIdx.y * 64 + c < F) atomicAdd(dw + (static_cast<size_t>(oc) * F + blockIdx.y * 64 + c) * 9 + t, s);
+    }
+    if (threadIdx.x == 0 && blockIdx.y == 0) {
+      float s = 0.f;
+      for (int k = 0; k < 8; ++k) s += redb[k];
+      atomicAdd(db + oc, s);
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------- PixelShuffle adjoint
+// src: PNHWC (2H,2W) with C channels (gradient at the shuffled resolution, already masked);
+// dst: PNHWC (H,W) with 4C channels in packed order n = (2i+j)*C + c.  One thread = 8 channels.
+__global__ void unshuffle_kernel(const __nv_bfloat16* __restrict__ src, int s_cstride, int s_coff, int B, int H, int W,
+                                 int Cc, __nv_bfloat16* __restrict__ dst, int d_cstride, int d_coff) {
+  const int groups = Cc / 8;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long total = 1LL * B * H * W * 4 * groups;
+  if (idx >= total) return;
+  const int g = int(idx % groups);
+  long long r = idx / groups;
+  const int sub = int(r % 4); r /= 4;
+  const int px = int(r % W); r /= W;
+  const int py = int(r % H);
+  const int b = int(r / H);
+  const size_t srow = (static_cast<size_t>(b) * (2 * H + 1) + 2 * py + (sub >> 1)) * (2 * W + 1) + 2 * px + (sub & 1);
+  const size_t drow = (static_cast<size_t>(b) * (H + 1) + py) * (W + 1) + px;
+  *reinterpret_cast<uint4*>(dst + drow * d_cstride + d_coff + sub * Cc + g * 8) =
+      *reinterpret_cast<const uint4*>(src + srow * s_cstride + s_coff + g * 8);
+}
+
+}  // namespace srb
+
+// ================================================================== C ABI
+using namespace srb;
+#define SRB_LAUNCH_CHECK(name)                                         \
+  do {                                                                 \
+    cudaError_t e_ = cudaGetLastError();                               \
+    if (e_ != cudaSuccess) return set_cuda_error(name " launch", e_);  \
+  } while (0)
+
+extern "C" int srb_conv_in_fwd(const float* img, int B, int Cimg, int H, int W, float multiplier, float power,
+                               const float* w, const float* bias, int F, void* y, int y_cstride, int y_coff, void* y2,
+                               int y2_cstride, int y2_coff, void* stream) {
+  if (F % 8 || (y_cstride % 8) || (y_coff % 8)) return set_error("conv_in: F and channel offsets must be multiples of 8");
+  const long long total = 1LL * B * H * W * (F / 8);
+  conv_in_fwd_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      img, B, Cimg, H, W, multiplier, power, w, bias, F, (__nv_bfloat16*)y, y_cstride, y_coff, (__nv_bfloat16*)y2,
+      y2_cstride, y2_coff);
+  SRB_LAUNCH_CHECK("conv_in_fwd");
+  return 0;
+}
+
+extern "C" int srb_conv_in_bwd(const float* img, int B, int Cimg, int H, int W, float multiplier, float power,
+                               const void* g, int g_cstride, int g_coff, int F, float* dw, float* db, void* stream) {
+  if (Cimg > 4) return set_error("conv_in_bwd: at most 4 image channels");
+  cudaMemsetAsync(dw, 0, sizeof(float) * F * Cimg * 9, (cudaStream_t)stream);
+  cudaMemsetAsync(db, 0, sizeof(float) * F, (cudaStream_t)stream);
+  const long long npix = 1LL * B * H * W;
+  int blocks = 4 * sm_count();
+  int ppb = ceil_div(npix, blocks); if (ppb < 64) ppb = 64;
+  dim3 grid(ceil_div(npix, ppb), (F + 63) / 64);
+  conv_in_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, Cimg, H, W, multiplier, power,
+                                                             (const __nv_bfloat16*)g, g_cstride, g_coff, F, dw, db, ppb);
+  SRB_LAUNCH_CHECK("conv_in_bwd");
+  return 0;
+}
+
+extern "C" int srb_conv_out_fwd(const void* x, int x_cstride, int x_coff, int B, int H, int W, int F, const float* w,
+                                const float* bias, int Cimg, float multiplier, float power, float thres, int training,
+                                float* out, float* srs, float* z, void* stream) {
+  if (F % 64) return set_error("conv_out: F must be a multiple of 64");
+  const long long threads = 1LL * B * H * W * 32;
+  conv_out_fwd_kernel<<<ceil_div(threads, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, x_cstride, x_coff, B, H, W, F, w, bias, Cimg, 1.f / multiplier, power, thres, training,
+      out, srs, z);
+  SRB_LAUNCH_CHECK("conv_out_fwd");
+  return 0;
+}
+
+extern "C" int srb_conv_out_bwd(const float* z, const float* g_out, const float* g_srs, int B, int Cimg, int H, int W,
+                                float multiplier, float power, float thres, int training, const float* w, int F,
+                                const void* act, int act_cstride, int act_coff, float slope, float* gz_scratch,
+                                void* gy, int gy_cstride, int gy_coff, float* dw, float* db, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long n = 1LL * B * Cimg * H * W;
+  head_bwd_kernel<<<ceil_div(n, 256), 256, 0, st>>>(z, g_out, g_srs, n, 1.f / multiplier, power, thres, training,
+                                                    gz_scratch);
+  SRB_LAUNCH_CHECK("head_bwd");
+  const long long total = 1LL * B * H * W * (F / 8);
+  conv_out_dgrad_kernel<<<ceil_div(total, 256), 256, 0, st>>>(gz_scratch, B, Cimg, H, W, w, F,
+                                                              (const __nv_bfloat16*)act, act_cstride, act_coff, slope,
+                                                              (__nv_bfloat16*)gy, gy_cstride, gy_coff);
+  SRB_LAUNCH_CHECK("conv_out_dgrad");
+  cudaMemsetAsync(dw, 0, sizeof(float) * Cimg * F * 9, st);
+  cudaMemsetAsync(db, 0, sizeof(float) * Cimg, st);
+  const long long npix = 1LL * B * H * W;
+  int ppb = ceil_div(npix, 4 * sm_count()); if (ppb < 64) ppb = 64;
+  dim3 grid(ceil_div(npix, ppb), F / 64);
+  conv_out_wgrad_kernel<<<grid, 256, 0, st>>>(gz_scratch, B, Cimg, H, W, (const __nv_bfloat16*)act, act_cstride,
+                                              act_coff, F, dw, db, ppb);
+  SRB_LAUNCH_CHECK("conv_out_wgrad");
+  return 0;
+}
+
+extern "C" int srb_unshuffle2(const void* src, int s_cstride, int s_coff, int B, int H, int W, int C, void* dst,
+                              int d_cstride, int d_coff, void* stream) {
+  if (C % 8) return set_error("unshuffle: C must be a multiple of 8");
+  const long long total = 1LL * B * H * W * 4 * (C / 8);
+  unshuffle_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)src, s_cstride, s_coff, B, H, W, C, (__nv_bfloat16*)dst, d_cstride, d_coff);
+  SRB_LAUNCH_CHECK("unshuffle");
+  return 0;
+}

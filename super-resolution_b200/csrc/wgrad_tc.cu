@@ -1,0 +1,260 @@
+// K3: weight gradient of the 3x3 convolution on tcgen05 tensor cores (sm_100a).
+// Replaces the filter half of aten::convolution_backward for every generator conv (autograd of
+// models.py:19,67,87,97).
+//
+//   dW[co][ci][t] = alpha * sum_q  X[q][ci] * GZ[q - s_t][co],      s_t = dy*(W+1) + dx   (PNHWC flat rows)
+//
+// GEMM view: the reduction (K) dimension is the flat pixel index, so both operands are "MN-major" in shared
+// memory exactly as TMA delivers PNHWC rows (128 B = 64 channels per pixel, 128B swizzle):
+//   A = X tile    [K = 64 pixels][M = 128 input channels]  (two 64-channel TMA boxes, LBO = box size)
+//   B = GZ window [K = 64 pixels][N = 192 = 3 x 64]        the three 64-wide N blocks are the SAME smem
+//       window advanced by one pixel row each (LBO = 128 B): N block j is tap dx = 1 - j.  One MMA therefore
+//       produces three taps of one filter row; dy selects the window's row offset.
+// Work item = (pair of input-channel blocks, dy, 64-wide output-channel block, K split).  Each CTA accumulates
+// its whole K range in 192 TMEM columns, then writes a partial [3 taps][128 ci][64 co] fp32 tile to the
+// workspace; a second kernel reduces the K splits, scales, and scatters to OIHW (state_dict layout).
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace srb {
+
+constexpr int kWgThreads = 192;
+constexpr int kWgKc = 64;                       // pixels per pipeline stage
+constexpr int kWgStages = 6;
+constexpr int kWgXBytes = 2 * kWgKc * 128;      // two 64-channel boxes
+constexpr int kWgGRows = kWgKc + 8;
+constexpr int kWgGBytes = kWgGRows * 128;
+constexpr int kWgStageBytes = kWgXBytes + kWgGBytes;
+
+struct WgradParams {
+  int R, pitch;
+  int cin, cout;
+  int n_cp;          // ceil(cin / 128)
+  int n_cb;          // cout / 64
+  int splits;        // K splits
+  int chunks_per_split;
+  int x_coff, gy_coff;
+  float* ws;         // [splits][9][n_cp*128][cout]
+  int base_offset_mode;
+};
+
+__global__ void __launch_bounds__(kWgThreads, 1)
+wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_g,
+                   const WgradParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgStages * kWgStageBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + kWgStages;
+  uint64_t* done = empty + kWgStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // decode work item
+  int w = blockIdx.x;
+  const int split = w % p.splits; w /= p.splits;
+  const int dyi = w % 3; w /= 3;                 // dy = dyi - 1
+  const int cb = w % p.n_cb; w /= p.n_cb;
+  const int cp = w;
+  const int dy = dyi - 1;
+  const int n_chunks_total = (p.R + kWgKc - 1) / kWgKc;
+  const int c_begin = split * p.chunks_per_split;
+  int c_end = c_begin + p.chunks_per_split;
+  if (c_end > n_chunks_total) c_end = n_chunks_total;
+  const int n_chunks = c_end > c_begin ? c_end - c_begin : 0;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_g);
+    for (int i = 0; i < kWgStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 256);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t s = 0, ph = 0;
+      for (int c = 0; c < n_chunks; ++c) {
+        const int k0 = (c_begin + c) * kWgKc;
+        mbar_wait(&empty[s], ph ^ 1, 11);
+        mbar_expect_tx(&full[s], kWgStageBytes);
+        uint8_t* st = smem + s * kWgStageBytes;
+        tma_load_2d(st, &tmap_x, p.x_coff + cp * 128, k0, &full[s]);
+        tma_load_2d(st + kWgKc * 128, &tmap_x, p.x_coff + cp * 128 + 64, k0, &full[s]);
+        tma_load_2d(st + kWgXBytes, &tmap_g, p.gy_coff + cb * 64, k0 - dy * p.pitch - 1, &full[s]);
+        if (++s == kWgStages) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc_bf16(128, 192, 1, 1);
+    uint32_t s = 0, ph = 0;
+    for (int c = 0; c < n_chunks; ++c) {
+      mbar_wait(&full[s], ph, 12);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t xa = smem_u32(smem + s * kWgStageBytes);
+        const uint32_t ga = xa + kWgXBytes;
+#pragma unroll
+        for (int k = 0; k < kWgKc / 16; ++k) {
+          const uint64_t ad = make_sw128_desc(xa + k * 2048, kWgKc * 128, 1024, 0);
+          const uint64_t bd = make_sw128_desc(ga + k * 2048, 128, 1024, p.base_offset_mode);
+          umma_bf16(tmem_base, ad, bd, idesc, (c | k) != 0);
+        }
+        umma_commit(&empty[s]);
+        if (c == n_chunks - 1) umma_commit(done);
+      }
+      __syncwarp();
+      if (++s == kWgStages) { s = 0; ph ^= 1; }
+    }
+  } else {
+    const int lg = warp & 3;
+    const int row = lg * 32 + lane;               // M index = input channel within the pair
+    const int ci = cp * 128 + row;
+    const int cin_pad = p.n_cp * 128;
+    if (n_chunks > 0) {
+      mbar_wait(done, 0, 13);
+      tc_fence_after();
+    }
+#pragma unroll 1
+    for (int j = 0; j < 3; ++j) {
+      const int t = dyi * 3 + (2 - j);            // dx = 1 - j  ->  kx = dx + 1 = 2 - j
+      float* dst = p.ws + ((static_cast<size_t>(split) * 9 + t) * cin_pad + ci) * p.cout + cb * 64;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t acc[32];
+        if (n_chunks > 0) {
+          tmem_ld32(tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + j * 64 + half * 32, acc);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc[i] = 0u;
+        }
+        float4* d4 = reinterpret_cast<float4*>(dst + half * 32);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          d4[i] = make_float4(__uint_as_float(acc[4 * i]), __uint_as_float(acc[4 * i + 1]),
+                              __uint_as_float(acc[4 * i + 2]), __uint_as_float(acc[4 * i + 3]));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
+// Sum the K splits, scale, and scatter to OIHW.  One thread per (t, ci, co); co fastest so workspace reads coalesce.
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, int cin, int cin_pad, int cout,
+                                    float alpha, int accumulate, int unshuffle, float* __restrict__ dw) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long total = 9LL * cin * cout;
+  if (idx >= total) return;
+  const int co = int(idx % cout);
+  long long r = idx / cout;
+  const int ci = int(r % cin);
+  const int t = int(r / cin);
+  float s = 0.f;
+  for (int sp = 0; sp < splits; ++sp) s += ws[((static_cast<size_t>(sp) * 9 + t) * cin_pad + ci) * cout + co];
+  s *= alpha;
+  const int cq = cout / 4;
+  const int co_dst = unshuffle ? (4 * (co % cq) + co / cq) : co;
+  float* d = dw + (static_cast<size_t>(co_dst) * cin + ci) * 9 + t;
+  *d = accumulate ? *d + s : s;
+}
+
+// dbias[co] = alpha * sum over all flat rows of gy[:, co]; one block per 64 channels... small and bandwidth-bound.
+__global__ void colsum_kernel(const __nv_bfloat16* __restrict__ g, int R, int cstride, int coff, int cout, float alpha,
+                              int accumulate, int unshuffle, float* __restrict__ dbias) {
+  // block = 256 threads = 8 row-lanes x 32 channel-pairs; grid.x = cout/64, grid.y = row slices
+  const int cpair = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int c0 = blockIdx.x * 64 + cpair * 2;
+  float s0 = 0.f, s1 = 0.f;
+  for (long long q = blockIdx.y * 8 + rl; q < R; q += 8LL * gridDim.y) {
+    const uint32_t v = *reinterpret_cast<const uint32_t*>(g + q * cstride + coff + c0);
+    s0 += bf16lo(v); s1 += bf16hi(v);
+  }
+  __shared__ float red[8][64];
+  red[rl][cpair * 2] = s0; red[rl][cpair * 2 + 1] = s1;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float s = 0.f;
+    for (int i = 0; i < 8; ++i) s += red[i][threadIdx.x];
+    const int co = blockIdx.x * 64 + threadIdx.x;
+    const int cq = cout / 4;
+    const int co_dst = unshuffle ? (4 * (co % cq) + co / cq) : co;
+    atomicAdd(dbias + co_dst, alpha * s);
+  }
+}
+
+static void wgrad_plan(long long R, int cin, int cout, int* splits, int* chunks_per_split) {
+  const int n_cp = (cin + 127) / 128, n_cb = cout / 64;
+  const int units = n_cp * n_cb * 3;
+  const int chunks = int((R + kWgKc - 1) / kWgKc);
+  int s = (2 * sm_count() + units - 1) / units;       // ~2 CTAs worth of work items per SM
+  const int max_s = (chunks + 7) / 8;                 // at least 8 chunks per split
+  if (s > max_s) s = max_s;
+  if (s < 1) s = 1;
+  int cps = (chunks + s - 1) / s;
+  s = (chunks + cps - 1) / cps;
+  *splits = s; *chunks_per_split = cps;
+}
+
+int wgrad3x3_tc_launch(const srb_wgrad3x3_args* a, cudaStream_t stream) {
+  const int pitch = a->W + 1, P = (a->H + 1) * (a->W + 1);
+  const long long R = 1LL * a->batch * P;
+  if (R <= 0 || R > 0x7fffffffLL) return set_error("wgrad3x3: bad geometry");
+  if ((a->x_cstride % 8) || (a->gy_cstride % 8) || (a->x_coff % 8) || (a->gy_coff % 8))
+    return set_error("wgrad3x3: channel strides/offsets must keep 16-byte alignment");
+  int splits, cps;
+  wgrad_plan(R, a->cin, a->cout, &splits, &cps);
+  const int n_cp = (a->cin + 127) / 128, n_cb = a->cout / 64;
+  const size_t need = static_cast<size_t>(splits) * 9 * n_cp * 128 * a->cout * sizeof(float);
+  if (!a->workspace || a->workspace_bytes < need) return set_error("wgrad3x3: workspace too small");
+
+  CUtensorMap tx, tg;
+  if (make_tmap_2d_bf16(&tx, a->x, (uint64_t)a->x_cstride, (uint64_t)R, (uint64_t)a->x_cstride * 2, 64, kWgKc)) return 1;
+  if (make_tmap_2d_bf16(&tg, a->gy, (uint64_t)a->gy_cstride, (uint64_t)R, (uint64_t)a->gy_cstride * 2, 64, kWgGRows)) return 1;
+
+  WgradParams p{};
+  p.R = (int)R; p.pitch = pitch; p.cin = a->cin; p.cout = a->cout; p.n_cp = n_cp; p.n_cb = n_cb;
+  p.splits = splits; p.chunks_per_split = cps; p.x_coff = a->x_coff; p.gy_coff = a->gy_coff;
+  p.ws = (float*)a->workspace; p.base_offset_mode = a->flags & 1;
+
+  static bool attr = false;
+  const size_t smem = 1024 + size_t(kWgStages) * kWgStageBytes + 256;
+  if (!attr) { cudaFuncSetAttribute(wgrad3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr = true; }
+  const int grid = n_cp * n_cb * 3 * splits;
+  wgrad3x3_tc_kernel<<<grid, kWgThreads, smem, stream>>>(tx, tg, p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error("wgrad3x3_tc launch", e);
+  const long long total = 9LL * a->cin * a->cout;
+  wgrad_reduce_kernel<<<ceil_div(total, 256), 256, 0, stream>>>(p.ws, splits, a->cin, n_cp * 128, a->cout, a->alpha,
+                                                                a->accumulate, a->unshuffle, a->dw);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error("wgrad_reduce launch", e);
+  if (a->dbias) {
+    if (!a->accumulate) cudaMemsetAsync(a->dbias, 0, sizeof(float) * a->cout, stream);
+    int slices = int(R / 2048); if (slices < 1) slices = 1; if (slices > 64) slices = 64;
+    dim3 g(a->cout / 64, slices);
+    colsum_kernel<<<g, 256, 0, stream>>>((const __nv_bfloat16*)a->gy, (int)R, a->gy_cstride, a->gy_coff, a->cout,
+                                         a->alpha, a->accumulate, a->unshuffle, a->dbias);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return set_cuda_error("colsum launch", e);
+  }
+  return 0;
+}
+
+}  // namespace srb
+
+extern "C" size_t srb_wgrad3x3_workspace_bytes(int batch, int H, int W, int cin, int cout) {
+  int splits, cps;
+  srb::wgrad_plan(1LL * batch * (H + 1) * (W + 1), cin, cout, &splits, &cps);
+  return static_cast<size_t>(splits) * 9 * ((cin + 127) / 128) * 128 * cout * sizeof(float);
+}

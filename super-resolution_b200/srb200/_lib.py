@@ -1,0 +1,124 @@
+"""ctypes binding of libsrb200.so (include/srb200.h).  No torch types cross this boundary:
+tensors are passed as raw device pointers, the stream as a void*.
+
+The library is built in-tree by ``build()`` (nvcc, sm_100a only).  There is no CPU or
+torch fallback: if the shared object is missing or a call fails, a RuntimeError whose
+text contains "CUDA" is raised (the reference's handlers at esrgan.py:829-836 and
+hyper_search.py:108-110 key on that).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import threading
+
+PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(PKG_DIR, "csrc")
+LIB_PATH = os.path.join(PKG_DIR, "libsrb200.so")
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-shared"]
+
+ACT_NONE, ACT_LRELU, ACT_LRELU_MASK = 0, 1, 2
+STORE_PLAIN, STORE_SHUFFLE = 0, 1
+IMPL_TCGEN05, IMPL_NAIVE = 0, 1
+
+
+class Conv3x3Args(C.Structure):
+    _fields_ = [
+        ("batch", C.c_int), ("H", C.c_int), ("W", C.c_int),
+        ("x", C.c_void_p), ("x_cstride", C.c_int), ("x_coff", C.c_int), ("cin", C.c_int),
+        ("w", C.c_void_p), ("bias", C.c_void_p), ("cout", C.c_int),
+        ("y", C.c_void_p), ("y_cstride", C.c_int), ("y_coff", C.c_int),
+        ("store_mode", C.c_int), ("alpha", C.c_float), ("act", C.c_int), ("slope", C.c_float),
+        ("mask", C.c_void_p), ("mask_cstride", C.c_int), ("mask_coff", C.c_int),
+        ("res1", C.c_void_p), ("res1_cstride", C.c_int), ("res1_coff", C.c_int), ("res1_scale", C.c_float),
+        ("res2", C.c_void_p), ("res2_cstride", C.c_int), ("res2_coff", C.c_int), ("res2_scale", C.c_float),
+        ("impl", C.c_int), ("flags", C.c_int),
+    ]
+
+
+class Wgrad3x3Args(C.Structure):
+    _fields_ = [
+        ("batch", C.c_int), ("H", C.c_int), ("W", C.c_int),
+        ("x", C.c_void_p), ("x_cstride", C.c_int), ("x_coff", C.c_int), ("cin", C.c_int),
+        ("gy", C.c_void_p), ("gy_cstride", C.c_int), ("gy_coff", C.c_int), ("cout", C.c_int),
+        ("dw", C.c_void_p), ("dbias", C.c_void_p), ("alpha", C.c_float),
+        ("accumulate", C.c_int), ("unshuffle", C.c_int),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+        ("impl", C.c_int), ("flags", C.c_int),
+    ]
+
+
+def sources():
+    return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh")))
+
+
+def needs_build() -> bool:
+    if not os.path.exists(LIB_PATH):
+        return True
+    t = os.path.getmtime(LIB_PATH)
+    hdr = os.path.join(os.path.dirname(PKG_DIR), "include", "srb200.h")
+    return any(os.path.getmtime(s) > t for s in sources() + [hdr])
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile csrc/srb200_all.cu (unity build) into libsrb200.so for sm_100a."""
+    if not force and not needs_build():
+        return LIB_PATH
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+          ["-o", LIB_PATH, os.path.join(CSRC, "srb200_all.cu")]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("CUDA extension build failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(r.stderr)
+    return LIB_PATH
+
+
+_lib = None
+_lock = threading.Lock()
+
+_SIGS = {
+    "srb_last_error": (C.c_char_p, []),
+    "srb_abi_version": (C.c_int, []),
+    "srb_read_fault": (C.c_int, [C.POINTER(C.c_uint)]),
+    "srb_conv3x3": (C.c_int, [C.POINTER(Conv3x3Args), C.c_void_p]),
+    "srb_pack_conv3x3_fwd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
+    "srb_pack_conv3x3_dgrad": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
+                                         C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "srb_wgrad3x3": (C.c_int, [C.POINTER(Wgrad3x3Args), C.c_void_p]),
+    "srb_wgrad3x3_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "srb_probe_mma_rate": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                     C.c_void_p]),
+}
+
+
+def exported_symbols():
+    return list(_SIGS)
+
+
+def lib():
+    """Load libsrb200.so (once).  Fails loudly when it is absent: there is no fallback path."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise RuntimeError(
+                        "CUDA extension libsrb200.so is not built (run `python -c 'import __graft_entry__ as g; "
+                        "g.build()'`); super-resolution_b200 has no CPU fallback")
+                l = C.CDLL(LIB_PATH)
+                for name, (res, args) in _SIGS.items():
+                    fn = getattr(l, name)
+                    fn.restype = res
+                    fn.argtypes = args
+                _lib = l
+    return _lib
+
+
+def check(status: int, what: str = "") -> None:
+    if status != 0:
+        msg = lib().srb_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"{msg} [{what}]" if what else msg)

@@ -1,0 +1,133 @@
+"""Tensor-level wrappers over the C ABI.  torch is used for device memory and streams only."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib as L
+
+Tensor = torch.Tensor
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _require_cuda(t: Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"CUDA tensor required for {name}: super-resolution_b200 has no CPU path")
+
+
+# ------------------------------------------------------------------ PNHWC activation buffers
+def pnhwc_zeros(batch: int, H: int, W: int, C_: int, device) -> Tensor:
+    """bf16 [batch, H+1, W+1, C] with the zero pad row/column (include/srb200.h)."""
+    return torch.zeros(batch, H + 1, W + 1, C_, dtype=torch.bfloat16, device=device)
+
+
+def to_pnhwc(x: Tensor, C_total: Optional[int] = None, coff: int = 0) -> Tensor:
+    """NCHW float -> PNHWC bf16 (test / glue helper, not on the hot path)."""
+    B, Cc, H, W = x.shape
+    buf = pnhwc_zeros(B, H, W, C_total or Cc, x.device)
+    buf[:, :H, :W, coff:coff + Cc] = x.permute(0, 2, 3, 1).to(torch.bfloat16)
+    return buf
+
+
+def from_pnhwc(buf: Tensor, coff: int = 0, c: Optional[int] = None) -> Tensor:
+    """PNHWC bf16 -> NCHW fp32."""
+    B, Hp, Wp, Ct = buf.shape
+    c = Ct - coff if c is None else c
+    return buf[:, :Hp - 1, :Wp - 1, coff:coff + c].permute(0, 3, 1, 2).float().contiguous()
+
+
+# ------------------------------------------------------------------ weight packs
+def pack_fwd(w: Tensor, shuffle: bool = False, scale: float = 1.0, out: Optional[Tensor] = None) -> Tensor:
+    """fp32 OIHW -> bf16 [9][cin/64][cout][64]."""
+    _require_cuda(w, "pack_fwd")
+    cout, cin = w.shape[0], w.shape[1]
+    w = w.detach().contiguous().float()
+    if out is None:
+        out = torch.empty(9 * cin * cout, dtype=torch.bfloat16, device=w.device)
+    L.check(L.lib().srb_pack_conv3x3_fwd(w.data_ptr(), cout, cin, int(shuffle), float(scale), out.data_ptr(),
+                                         _stream()), "pack_fwd")
+    return out
+
+
+def pack_dgrad(w: Tensor, ci_off: int, n_out: int, out: Tensor, kb_dst: int, kb_total: int, *,
+               unshuffle: bool = False, scale: float = 1.0) -> Tensor:
+    """dgrad pack of forward weight ``w`` (fp32 OIHW) for input channels [ci_off, ci_off+n_out), written at
+    k-block ``kb_dst`` of ``out`` = bf16 [9][kb_total][n_out][64]."""
+    _require_cuda(w, "pack_dgrad")
+    cout, cin = w.shape[0], w.shape[1]
+    w = w.detach().contiguous().float()
+    L.check(L.lib().srb_pack_conv3x3_dgrad(w.data_ptr(), cout, cin, ci_off, n_out, int(unshuffle), float(scale),
+                                           out.data_ptr(), kb_dst, kb_total, _stream()), "pack_dgrad")
+    return out
+
+
+# ------------------------------------------------------------------ convolution
+def conv3x3(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Tensor], y: Tensor, y_coff: int, cout: int,
+            *, alpha: float = 1.0, act: int = L.ACT_NONE, slope: float = 0.01,
+            mask: Optional[Tuple[Tensor, int]] = None, res1: Optional[Tuple[Tensor, int, float]] = None,
+            res2: Optional[Tuple[Tensor, int, float]] = None, shuffle: bool = False, impl: int = L.IMPL_TCGEN05,
+            flags: int = 0) -> None:
+    """y[..., y_coff:y_coff+cout] = epilogue(conv3x3(x[..., x_coff:x_coff+cin])); x, y PNHWC bf16 buffers."""
+    _require_cuda(x, "conv3x3")
+    B, Hp, Wp, Cx = x.shape
+    a = L.Conv3x3Args()
+    a.batch, a.H, a.W = B, Hp - 1, Wp - 1
+    a.x, a.x_cstride, a.x_coff, a.cin = x.data_ptr(), Cx, x_coff, cin
+    a.w, a.bias, a.cout = wp.data_ptr(), _ptr(bias), cout
+    a.y, a.y_cstride, a.y_coff = y.data_ptr(), y.shape[-1], y_coff
+    a.store_mode = L.STORE_SHUFFLE if shuffle else L.STORE_PLAIN
+    if shuffle:
+        assert y.shape[1] == 2 * a.H + 1 and y.shape[2] == 2 * a.W + 1 and y.shape[0] == B
+    else:
+        assert y.shape[:3] == x.shape[:3]
+    a.alpha, a.act, a.slope = alpha, act, slope
+    if mask is not None:
+        a.mask, a.mask_cstride, a.mask_coff = mask[0].data_ptr(), mask[0].shape[-1], mask[1]
+    if res1 is not None:
+        a.res1, a.res1_cstride, a.res1_coff, a.res1_scale = res1[0].data_ptr(), res1[0].shape[-1], res1[1], res1[2]
+    if res2 is not None:
+        a.res2, a.res2_cstride, a.res2_coff, a.res2_scale = res2[0].data_ptr(), res2[0].shape[-1], res2[1], res2[2]
+    a.impl, a.flags = impl, flags
+    L.check(L.lib().srb_conv3x3(C.byref(a), _stream()), "conv3x3")
+
+
+def wgrad_workspace_bytes(batch: int, H: int, W: int, cin: int, cout: int) -> int:
+    return int(L.lib().srb_wgrad3x3_workspace_bytes(batch, H, W, cin, cout))
+
+
+def wgrad3x3(x: Tensor, x_coff: int, cin: int, gy: Tensor, gy_coff: int, cout: int, dw: Tensor,
+             dbias: Optional[Tensor], *, alpha: float = 1.0, accumulate: bool = False, unshuffle: bool = False,
+             workspace: Optional[Tensor] = None, impl: int = L.IMPL_TCGEN05, flags: int = 0) -> None:
+    """dw (fp32 OIHW) = alpha * sum_pixels gy (x) x; both PNHWC bf16 buffers of the same geometry."""
+    _require_cuda(x, "wgrad3x3")
+    B, Hp, Wp, Cx = x.shape
+    assert gy.shape[:3] == x.shape[:3]
+    assert dw.dtype == torch.float32 and dw.is_contiguous() and tuple(dw.shape) == (cout, cin, 3, 3)
+    a = L.Wgrad3x3Args()
+    a.batch, a.H, a.W = B, Hp - 1, Wp - 1
+    a.x, a.x_cstride, a.x_coff, a.cin = x.data_ptr(), Cx, x_coff, cin
+    a.gy, a.gy_cstride, a.gy_coff, a.cout = gy.data_ptr(), gy.shape[-1], gy_coff, cout
+    a.dw, a.dbias, a.alpha = dw.data_ptr(), _ptr(dbias), alpha
+    a.accumulate, a.unshuffle = int(accumulate), int(unshuffle)
+    if impl == L.IMPL_TCGEN05:
+        need = wgrad_workspace_bytes(B, a.H, a.W, cin, cout)
+        if workspace is None or workspace.numel() * workspace.element_size() < need:
+            workspace = torch.empty(need, dtype=torch.uint8, device=x.device)
+        a.workspace, a.workspace_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+    a.impl, a.flags = impl, flags
+    L.check(L.lib().srb_wgrad3x3(C.byref(a), _stream()), "wgrad3x3")
+
+
+def read_fault() -> int:
+    v = C.c_uint(0)
+    L.check(L.lib().srb_read_fault(C.byref(v)), "read_fault")
+    return int(v.value)
