@@ -111,6 +111,49 @@ typedef struct srb_wgrad3x3_args {
 int srb_wgrad3x3(const srb_wgrad3x3_args* a, void* stream);
 size_t srb_wgrad3x3_workspace_bytes(int batch, int H, int W, int cin, int cout);
 
+/* ---- bandwidth-bound ends of the generator (csrc/gen_edge.cu) ------------------------------------
+ * srb_conv_in_fwd : models.py:122-123  multiplier*x**power -> conv1; fp32 NCHW image -> PNHWC bf16 (two optional dsts)
+ * srb_conv_in_bwd : conv1 weight/bias gradient from g (+ g2, the long-skip gradient of models.py:126)
+ * srb_conv_out_fwd: models.py:99,131-135,114-118  conv3.2 / multiplier + output head; writes out, srs and z
+ * srb_conv_out_bwd: adjoint of the above: head, conv3.2 dgrad (masked by LeakyReLU' of conv3.0's activation,
+ *                   models.py:98) into a PNHWC bf16 buffer, conv3.2 weight/bias gradient
+ * srb_unshuffle2  : adjoint of nn.PixelShuffle(2) (models.py:89) in the packed channel order (2i+j)*C + c      */
+int srb_conv_in_fwd(const float* img, int B, int Cimg, int H, int W, float multiplier, float power, const float* w,
+                    const float* bias, int F, void* y, int y_cstride, int y_coff, void* y2, int y2_cstride,
+                    int y2_coff, void* stream);
+int srb_conv_in_bwd(const float* img, int B, int Cimg, int H, int W, float multiplier, float power, const void* g,
+                    int g_cstride, int g_coff, const void* g2, int g2_cstride, int g2_coff, int F, float* dw,
+                    float* db, void* stream);
+int srb_conv_out_fwd(const void* x, int x_cstride, int x_coff, int B, int H, int W, int F, const float* w,
+                     const float* bias, int Cimg, float multiplier, float power, float thres, int training,
+                     float* out, float* srs, float* z, void* stream);
+int srb_conv_out_bwd(const float* z, const float* g_out, const float* g_srs, int B, int Cimg, int H, int W,
+                     float multiplier, float power, float thres, int training, const float* w, int F, const void* act,
+                     int act_cstride, int act_coff, float slope, float* gz_scratch, void* gy, int gy_cstride,
+                     int gy_coff, float* dw, float* db, void* stream);
+int srb_unshuffle2(const void* src, int s_cstride, int s_coff, int B, int H, int W, int C, void* dst, int d_cstride,
+                   int d_coff, void* stream);
+
+/* ---- discriminator stack and SumPool2d (csrc/disc.cu), fp32 NCHW ---------------------------------
+ * srb_dconv_fwd/dgrad/wgrad: nn.Conv2d(k=3, padding=1, stride 1|2) of discriminator_block (models.py:140-146,168)
+ *   and the two halves of its backward; composed by the host into first and second derivatives (the gradient
+ *   penalty of esrgan.py:598-606 differentiates the input gradient again).
+ * srb_lrelu_fwd/bwd: nn.LeakyReLU(0.2) (models.py:143,145).   srb_sumpool_fwd/bwd: SumPool2d (models.py:297-305). */
+int srb_dconv_fwd(const float* x, const float* w, const float* bias, float* y, int B, int Cin, int H, int W, int Cout,
+                  int stride, void* stream);
+int srb_dconv_dgrad(const float* gy, const float* w, float* gx, int B, int Cin, int H, int W, int Cout, int stride,
+                    void* stream);
+int srb_dconv_wgrad(const float* gy, const float* x, float* dw, float* db, int B, int Cin, int H, int W, int Cout,
+                    int stride, void* stream);
+int srb_lrelu_fwd(const float* x, float* y, long long n, float slope, void* stream);
+int srb_lrelu_bwd(const float* g, const float* ref, float* gx, long long n, float slope, void* stream);
+int srb_sumpool_fwd(const float* x, float* y, int BC, int H, int W, int k, void* stream);
+int srb_sumpool_bwd(const float* gy, float* gx, int BC, int H, int W, int k, void* stream);
+
+/* Bring-up microbenchmark: sustained tcgen05.mma issue rate (csrc/probe.cu); not on the product path. */
+int srb_probe_mma_rate(int cta_group, int N, int iters, int a_row_shift, int mn_major, int b_lbo, int n_ctas,
+                       long long* cycles_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

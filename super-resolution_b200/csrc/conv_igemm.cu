@@ -177,10 +177,11 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         int ycoff = p.y_coff;
         if (p.store_mode == SRB_STORE_SHUFFLE) {
           const int img = q / p.P;
-          const int sub = nt & 3;               // (i,j) = (sub>>1, sub&1); Cy == 64
+          const int cblocks = p.n_ntiles >> 2;  // 64-wide blocks per shuffled output channel group (Cy / 64)
+          const int sub = nt / cblocks;         // (i,j) = (sub>>1, sub&1)
           yrow = static_cast<size_t>(img) * p.y_P + static_cast<size_t>(2 * py + (sub >> 1)) * p.y_pitch +
                  (2 * px + (sub & 1));
-          ycoff += (nt >> 2) * 64;
+          ycoff += (nt % cblocks) * 64;
         } else {
           yrow = static_cast<size_t>(q);
           ycoff += n0;
@@ -287,7 +288,7 @@ int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   if (a->cin % 64 || a->cout % 64 || a->cin <= 0 || a->cout <= 0) return set_error("conv3x3: channels must be multiples of 64");
   if ((a->x_cstride % 8) || (a->y_cstride % 8) || (a->x_coff % 64) || (a->y_coff % 8))
     return set_error("conv3x3: channel strides/offsets must keep 16-byte alignment");
-  if (a->store_mode == SRB_STORE_SHUFFLE && a->cout != 256) return set_error("conv3x3: shuffle store needs cout == 256");
+  if (a->store_mode == SRB_STORE_SHUFFLE && a->cout % 256) return set_error("conv3x3: shuffle store needs cout % 256 == 0");
   const int pitch = a->W + 1, P = (a->H + 1) * (a->W + 1);
   const long long R = 1LL * a->batch * P;
   if (R <= 0 || R > 0x7fffffffLL) return set_error("conv3x3: bad geometry");

@@ -42,7 +42,8 @@ __global__ void conv3x3_naive_kernel(const NaiveConvParams p) {
   else if (p.act == SRB_ACT_LRELU_MASK)
     v *= __bfloat162float(p.mask[q * p.mask_cstride + p.mask_coff + n]) > 0.f ? 1.f : p.slope;
   if (p.store_mode == SRB_STORE_SHUFFLE) {
-    const int sub = n / 64, c = n % 64;                      // packed channel order (2i+j)*64 + c
+    const int Cy = p.cout / 4;
+    const int sub = n / Cy, c = n % Cy;                      // packed channel order (2i+j)*Cy + c
     const long long img = q / p.P;
     const long long yrow = img * p.y_P + (long long)(2 * py + (sub >> 1)) * p.y_pitch + (2 * px + (sub & 1));
     p.y[yrow * p.y_cstride + p.y_coff + c] = __float2bfloat16(v);
@@ -53,8 +54,8 @@ __global__ void conv3x3_naive_kernel(const NaiveConvParams p) {
 
 int conv3x3_naive_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   if (a->cin % 64 || a->cout % 64) return set_error("conv3x3(naive): channels must be multiples of 64");
-  if (a->store_mode == SRB_STORE_SHUFFLE && a->cout != 256)
-    return set_error("conv3x3(naive): shuffle store needs cout == 256");
+  if (a->store_mode == SRB_STORE_SHUFFLE && a->cout % 256)
+    return set_error("conv3x3(naive): shuffle store needs cout % 256 == 0");
   NaiveConvParams p{};
   p.pitch = a->W + 1; p.P = (a->H + 1) * (a->W + 1); p.R = a->batch * p.P; p.H = a->H; p.W = a->W;
   p.KB = a->cin / 64; p.cout = a->cout; p.x_cstride = a->x_cstride; p.x_coff = a->x_coff;

@@ -55,7 +55,8 @@ __global__ void conv_in_fwd_kernel(const float* __restrict__ img, int B, int Cim
 // dW[f][c][t] += sum_p g[p][f] * xin[p + s_t][c];  db[f] += sum_p g[p][f].   grid.x = pixel chunks;
 // block = 256 threads = F(64) x 4 pixel lanes (F <= 64 per blockIdx.y slice).
 __global__ void conv_in_bwd_kernel(const float* __restrict__ img, int B, int Cimg, int H, int W, float multiplier,
-                                   float power, const __nv_bfloat16* __restrict__ g, int g_cstride, int g_coff, int F,
+                                   float power, const __nv_bfloat16* __restrict__ g, int g_cstride, int g_coff,
+                                   const __nv_bfloat16* __restrict__ g2, int g2_cstride, int g2_coff, int F,
                                    float* __restrict__ dw, float* __restrict__ db, int pix_per_block) {
   const int f = blockIdx.y * 64 + (threadIdx.x & 63);
   const int pl = threadIdx.x >> 6;
@@ -70,7 +71,8 @@ __global__ void conv_in_bwd_kernel(const float* __restrict__ img, int B, int Cim
   for (long long pidx = p0 + pl; pidx < p1; pidx += 4) {
     const int px = int(pidx % W); const int py = int((pidx / W) % H); const int b = int(pidx / (1LL * W * H));
     const size_t row = (static_cast<size_t>(b) * (H + 1) + py) * (W + 1) + px;
-    const float gv = f < F ? __bfloat162float(g[row * g_cstride + g_coff + f]) : 0.f;
+    float gv = f < F ? __bfloat162float(g[row * g_cstride + g_coff + f]) : 0.f;
+    if (g2 && f < F) gv += __bfloat162float(g2[row * g2_cstride + g2_coff + f]);
     bsum += gv;
     if (gv == 0.f) continue;
     for (int c = 0; c < Cc; ++c) {
@@ -308,7 +310,8 @@ extern "C" int srb_conv_in_fwd(const float* img, int B, int Cimg, int H, int W, 
 }
 
 extern "C" int srb_conv_in_bwd(const float* img, int B, int Cimg, int H, int W, float multiplier, float power,
-                               const void* g, int g_cstride, int g_coff, int F, float* dw, float* db, void* stream) {
+                               const void* g, int g_cstride, int g_coff, const void* g2, int g2_cstride, int g2_coff,
+                               int F, float* dw, float* db, void* stream) {
   if (Cimg > 4) return set_error("conv_in_bwd: at most 4 image channels");
   cudaMemsetAsync(dw, 0, sizeof(float) * F * Cimg * 9, (cudaStream_t)stream);
   cudaMemsetAsync(db, 0, sizeof(float) * F, (cudaStream_t)stream);
@@ -317,7 +320,8 @@ extern "C" int srb_conv_in_bwd(const float* img, int B, int Cimg, int H, int W, 
   int ppb = ceil_div(npix, blocks); if (ppb < 64) ppb = 64;
   dim3 grid(ceil_div(npix, ppb), (F + 63) / 64);
   conv_in_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, Cimg, H, W, multiplier, power,
-                                                             (const __nv_bfloat16*)g, g_cstride, g_coff, F, dw, db, ppb);
+                                                             (const __nv_bfloat16*)g, g_cstride, g_coff,
+                                                             (const __nv_bfloat16*)g2, g2_cstride, g2_coff, F, dw, db, ppb);
   SRB_LAUNCH_CHECK("conv_in_bwd");
   return 0;
 }

@@ -1,0 +1,331 @@
+"""Execution engine for GeneratorRRDB on the C ABI kernels (forward + hand-scheduled backward).
+
+Mirrors models.py:9-135 of the reference.  The module objects in ``models.py`` of this package only hold
+parameters (same names/shapes as the reference state_dict); this engine turns a forward into a fixed sequence of
+kernel launches over preallocated PNHWC bf16 buffers:
+
+* each DenseResidualBlock owns a growth buffer [B, h+1, w+1, 5F]; conv k reads channels [0, kF) and writes slot k
+  in place (no torch.cat, models.py:38); conv 5's epilogue applies ``out*res_scale + x`` (models.py:41) and, for
+  the third block of an RRDB, the outer ``*res_scale + x`` too (models.py:53), storing into slot 0 of the next
+  block's buffer;
+* backward mirrors it on a gradient growth buffer [g_out, gz5, gz4, ..., gz1]: the gradient of slot j is ONE
+  convolution over the already-final gradient slots with a concatenated transposed/flipped weight pack, so the
+  dense block's input gradients are never read-modify-written (hard part 2).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from . import _lib as L
+from . import ops
+
+Tensor = torch.Tensor
+G_SLOPE = 0.01      # nn.LeakyReLU() default (models.py:21,88,98)
+DRB_SCALE = 0.2     # DenseResidualBlock default res_scale; never overridden (models.py:49)
+
+PARAM_EPOCH = [0]   # bumped by srb200.optim.FusedAdam.step(); engines re-pack weights when it moves
+
+
+def _st() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+class _Bufs:
+    """Activation / gradient buffers for one (batch, h, w, training) shape."""
+    pass
+
+
+class GeneratorEngine:
+    def __init__(self, params: Dict[str, torch.nn.Parameter], *, channels: int, filters: int, num_res_blocks: int,
+                 num_upsample: int, res_scale: float, impl: int = L.IMPL_TCGEN05):
+        if filters % 64:
+            raise RuntimeError("CUDA srb200: GeneratorRRDB engine needs filters to be a multiple of 64")
+        if channels > 4:
+            raise RuntimeError("CUDA srb200: at most 4 image channels")
+        self.p = params
+        self.ch, self.F, self.nb, self.nup, self.rs = channels, filters, num_res_blocks, num_upsample, float(res_scale)
+        self.impl = impl
+        self._bufs: Dict[Tuple, _Bufs] = {}
+        self._pack_key = None
+        self._packs_bwd_ready = False
+        self._saved = None
+        self.names3x3 = self._conv_names()
+
+    # ------------------------------------------------------------------ parameter bookkeeping
+    def _conv_names(self) -> List[str]:
+        n = []
+        for i in range(self.nb):
+            for j in range(3):
+                for k in range(1, 6):
+                    n.append(f"res_blocks.{i}.dense_blocks.{j}.b{k}.0")
+        n.append("conv2")
+        n += [f"upsampling.{3 * u}" for u in range(self.nup)]
+        n.append("conv3.0")
+        return n
+
+    def _w(self, name: str) -> Tensor:
+        return self.p[name + ".weight"]
+
+    def _b(self, name: str) -> Tensor:
+        return self.p[name + ".bias"]
+
+    def _params_key(self):
+        dev = self._w("conv1").device
+        return (PARAM_EPOCH[0], str(dev), sum(p._version for p in self.p.values()),
+                self._w("conv2").data_ptr())
+
+    def _ensure_packs(self, need_bwd: bool) -> None:
+        key = self._params_key()
+        if key != self._pack_key:
+            self._build_fwd_packs()
+            self._pack_key = key
+            self._packs_bwd_ready = False
+        if need_bwd and not self._packs_bwd_ready:
+            self._build_bwd_packs()
+            self._packs_bwd_ready = True
+
+    def _build_fwd_packs(self) -> None:
+        dev = self._w("conv1").device
+        F_ = self.F
+        sizes = {}
+        total = 0
+        for n in self.names3x3:
+            w = self._w(n)
+            sizes[n] = (total, w.numel())
+            total += w.numel()
+        if getattr(self, "_fwd_flat", None) is None or self._fwd_flat.numel() != total or self._fwd_flat.device != dev:
+            self._fwd_flat = torch.empty(total, dtype=torch.bfloat16, device=dev)
+        self.wp: Dict[str, Tensor] = {}
+        self.bias_packed: Dict[str, Tensor] = {}
+        for n in self.names3x3:
+            off, cnt = sizes[n]
+            shuffle = n.startswith("upsampling.")
+            self.wp[n] = ops.pack_fwd(self._w(n), shuffle=shuffle, out=self._fwd_flat[off:off + cnt])
+            b = self._b(n).detach()
+            if shuffle:
+                cout = b.numel()
+                idx = torch.arange(cout, device=dev)
+                b = b[4 * (idx % (cout // 4)) + idx // (cout // 4)].contiguous()
+            self.bias_packed[n] = b.float().contiguous()
+
+    def _build_bwd_packs(self) -> None:
+        """dgrad packs.  Dense block: for output slot jj (0..4) one pack with K-blocks ordered like the gradient
+        growth buffer [g_out(conv5), gz4, ..., gz_{jj+1}]; conv5's block is pre-scaled by the residual scale."""
+        dev = self._w("conv1").device
+        F_, kbF = self.F, self.F // 64
+        self.wd: Dict[str, Tensor] = {}
+        for i in range(self.nb):
+            for j in range(3):
+                s5 = DRB_SCALE * (self.rs if j == 2 else 1.0)
+                base = f"res_blocks.{i}.dense_blocks.{j}."
+                for jj in range(5):
+                    nsrc = 5 - jj
+                    pack = torch.empty(9 * nsrc * F_ * F_, dtype=torch.bfloat16, device=dev)
+                    for kk in range(5, jj, -1):           # forward conv kk feeds slot jj
+                        ops.pack_dgrad(self._w(base + f"b{kk}.0"), jj * F_, F_, pack, (5 - kk) * kbF, nsrc * kbF,
+                                       scale=s5 if kk == 5 else 1.0)
+                    self.wd[base + f"slot{jj}"] = pack
+        for n in ["conv2", "conv3.0"]:
+            pack = torch.empty(9 * F_ * F_, dtype=torch.bfloat16, device=dev)
+            self.wd[n] = ops.pack_dgrad(self._w(n), 0, F_, pack, 0, kbF)
+        for u in range(self.nup):
+            n = f"upsampling.{3 * u}"
+            pack = torch.empty(9 * 4 * F_ * F_, dtype=torch.bfloat16, device=dev)
+            self.wd[n] = ops.pack_dgrad(self._w(n), 0, F_, pack, 0, 4 * kbF, unshuffle=True)
+
+    # ------------------------------------------------------------------ buffers
+    def _get_bufs(self, B: int, h: int, w: int, training: bool, dev) -> _Bufs:
+        key = (B, h, w, training, str(dev))
+        bf = self._bufs.get(key)
+        if bf is not None:
+            return bf
+        if len(self._bufs) > 4:
+            self._bufs.clear()
+        F_ = self.F
+        bf = _Bufs()
+        n_growth = 3 * self.nb if training else 4
+        bf.growth = [ops.pnhwc_zeros(B, h, w, 5 * F_, dev) for _ in range(max(n_growth, 1))]
+        bf.out1 = None if training else ops.pnhwc_zeros(B, h, w, F_, dev)
+        bf.trunk = ops.pnhwc_zeros(B, h, w, F_, dev)
+        bf.feat = ops.pnhwc_zeros(B, h, w, F_, dev)
+        bf.up = [ops.pnhwc_zeros(B, h << (u + 1), w << (u + 1), F_, dev) for u in range(self.nup)]
+        H, W = h << self.nup, w << self.nup
+        bf.hr = ops.pnhwc_zeros(B, H, W, F_, dev)
+        bf.out = torch.empty(B, self.ch, H, W, device=dev)
+        bf.srs = torch.empty(B, self.ch, H, W, device=dev)
+        bf.z = torch.empty(B, self.ch, H, W, device=dev)
+        if training:
+            bf.G = [ops.pnhwc_zeros(B, h, w, 5 * F_, dev) for _ in range(3)]
+            bf.g_s = ops.pnhwc_zeros(B, h, w, F_, dev)
+            bf.g_out1 = ops.pnhwc_zeros(B, h, w, F_, dev)
+            bf.g_hr = ops.pnhwc_zeros(B, H, W, F_, dev)
+            bf.g_up = [ops.pnhwc_zeros(B, h << (u + 1), w << (u + 1), F_, dev) for u in range(self.nup)]
+            bf.g_uns = [ops.pnhwc_zeros(B, h << u, w << u, 4 * F_, dev) for u in range(self.nup)]
+            bf.g_feat = [ops.pnhwc_zeros(B, h << u, w << u, F_, dev) for u in range(1, self.nup)]
+            bf.gz_scratch = torch.empty(B, self.ch, H, W, device=dev)
+            ws = 0
+            for (hh, ww, cin, cout) in ([(h, w, k * F_, F_) for k in range(1, 6)]
+                                        + [(h << u, w << u, F_, 4 * F_) for u in range(self.nup)] + [(H, W, F_, F_)]):
+                ws = max(ws, ops.wgrad_workspace_bytes(B, hh, ww, cin, cout))
+            bf.ws = torch.empty(ws, dtype=torch.uint8, device=dev)
+            gp = [(n, p) for n, p in self.p.items() if n not in ("power", "multiplier")]
+            bf.gflat = torch.zeros(sum(p.numel() for _, p in gp), device=dev)
+            bf.grads = {}
+            off = 0
+            for n, p in gp:
+                bf.grads[n] = bf.gflat[off:off + p.numel()].view(p.shape)
+                off += p.numel()
+        self._bufs[key] = bf
+        return bf
+
+    # ------------------------------------------------------------------ forward
+    def _conv(self, x, x_coff, cin, name, y, y_coff, cout, **kw):
+        ops.conv3x3(x, x_coff, cin, self.wp[name], self.bias_packed[name], y, y_coff, cout, impl=self.impl, **kw)
+
+    def forward(self, img: Tensor, *, power: float, multiplier: float, thres: float, training: bool,
+                save_for_backward: bool) -> Tuple[Tensor, Tensor]:
+        """models.py:120-135.  ``img`` fp32 [B, channels, h, w] on the GPU.  Returns (out, srs) as fresh tensors."""
+        if not img.is_cuda:
+            raise RuntimeError("CUDA tensor required: super-resolution_b200 has no CPU path for GeneratorRRDB")
+        img = img.detach().float().contiguous()
+        B, ch, h, w = img.shape
+        if ch != self.ch:
+            raise RuntimeError(f"CUDA srb200: expected {self.ch} image channels, got {ch}")
+        self._ensure_packs(save_for_backward)
+        bf = self._get_bufs(B, h, w, save_for_backward, img.device)
+        F_, lib = self.F, L.lib()
+        g = bf.growth
+        ng = len(g)
+        # conv1 (models.py:122-123) -> slot 0 of the first growth buffer (+ a copy for the long skip at inference)
+        y2 = bf.out1
+        L.check(lib.srb_conv_in_fwd(img.data_ptr(), B, ch, h, w, float(multiplier), float(power),
+                                    self._w("conv1").data_ptr(), self._b("conv1").data_ptr(), F_,
+                                    g[0].data_ptr(), 5 * F_, 0, y2.data_ptr() if y2 is not None else None, F_, 0,
+                                    _st()), "conv_in_fwd")
+        # RRDB trunk (models.py:124)
+        d = 0
+        for i in range(self.nb):
+            first = d
+            for j in range(3):
+                cur = g[d % ng]
+                base = f"res_blocks.{i}.dense_blocks.{j}."
+                for k in range(1, 5):
+                    self._conv(cur, 0, k * F_, base + f"b{k}.0", cur, k * F_, F_, act=L.ACT_LRELU, slope=G_SLOPE)
+                last = (i == self.nb - 1 and j == 2)
+                dst, dst_off = (bf.trunk, 0) if last else (g[(d + 1) % ng], 0)
+                if j < 2:
+                    self._conv(cur, 0, 5 * F_, base + "b5.0", dst, dst_off, F_, alpha=DRB_SCALE, res1=(cur, 0, 1.0))
+                else:
+                    self._conv(cur, 0, 5 * F_, base + "b5.0", dst, dst_off, F_, alpha=DRB_SCALE * self.rs,
+                               res1=(cur, 0, self.rs), res2=(g[first % ng], 0, 1.0))
+                d += 1
+        if self.nb == 0:
+            raise RuntimeError("CUDA srb200: num_res_blocks must be >= 1")
+        # conv2 + long skip (models.py:125-126)
+        out1 = (g[0], 0, 1.0) if bf.out1 is None else (bf.out1, 0, 1.0)
+        self._conv(bf.trunk, 0, F_, "conv2", bf.feat, 0, F_, res1=out1)
+        # upsampling (models.py:127 / 85-91): conv F->4F, LeakyReLU, PixelShuffle(2) fused in the epilogue store
+        cur = bf.feat
+        for u in range(self.nup):
+            self._conv(cur, 0, F_, f"upsampling.{3 * u}", bf.up[u], 0, 4 * F_, act=L.ACT_LRELU, slope=G_SLOPE,
+                       shuffle=True)
+            cur = bf.up[u]
+        # conv3.0 + LeakyReLU (models.py:97-98)
+        self._conv(cur, 0, F_, "conv3.0", bf.hr, 0, F_, act=L.ACT_LRELU, slope=G_SLOPE)
+        # conv3.2, /multiplier and the output head (models.py:99,131-135,114-118)
+        H, W = h << self.nup, w << self.nup
+        out = torch.empty(B, ch, H, W, device=img.device)
+        srs = torch.empty(B, ch, H, W, device=img.device)
+        L.check(lib.srb_conv_out_fwd(bf.hr.data_ptr(), F_, 0, B, H, W, F_, self._w("conv3.2").data_ptr(),
+                                     self._b("conv3.2").data_ptr(), ch, float(multiplier), float(power), float(thres),
+                                     int(training), out.data_ptr(), srs.data_ptr(), bf.z.data_ptr(), _st()),
+                "conv_out_fwd")
+        if save_for_backward:
+            self._saved = dict(img=img, bf=bf, power=float(power), multiplier=float(multiplier), thres=float(thres),
+                               training=bool(training), key=self._pack_key)
+        return out, srs
+
+    # ------------------------------------------------------------------ backward
+    def _wgrad(self, bf, x, cin, gy, gy_coff, cout, name, alpha=1.0, unshuffle=False):
+        ops.wgrad3x3(x, 0, cin, gy, gy_coff, cout, bf.grads[name + ".weight"], bf.grads[name + ".bias"], alpha=alpha,
+                     unshuffle=unshuffle, workspace=bf.ws, impl=self.impl)
+
+    def _dconv(self, x, cin, pack, y, y_coff, cout, **kw):
+        ops.conv3x3(x, 0, cin, pack, None, y, y_coff, cout, impl=self.impl, **kw)
+
+    def backward(self, g_out: Optional[Tensor], g_srs: Optional[Tensor]) -> Dict[str, Tensor]:
+        """Gradients of every parameter for the last ``forward(save_for_backward=True)``, given d loss / d out and
+        d loss / d srs (fp32 [B, ch, H, W] or None).  Returns name -> fp32 tensor views of one flat buffer (valid
+        until the next backward of the same shape)."""
+        sv = self._saved
+        if sv is None:
+            raise RuntimeError("CUDA srb200: backward called without a saved forward")
+        if sv["key"] != self._params_key():
+            raise RuntimeError("CUDA srb200: parameters changed between forward and backward")
+        bf, img = sv["bf"], sv["img"]
+        B, ch, h, w = img.shape
+        F_, lib = self.F, L.lib()
+        H, W = h << self.nup, w << self.nup
+        go = g_out.detach().float().contiguous() if g_out is not None else None
+        gs = g_srs.detach().float().contiguous() if g_srs is not None else None
+        top_in = bf.up[-1] if self.nup else bf.feat
+        # conv3.2 + head (models.py:99,131-135): gradient of conv3.0's activation, masked by LeakyReLU'
+        L.check(lib.srb_conv_out_bwd(bf.z.data_ptr(), go.data_ptr() if go is not None else None,
+                                     gs.data_ptr() if gs is not None else None, B, ch, H, W, sv["multiplier"],
+                                     sv["power"], sv["thres"], int(sv["training"]), self._w("conv3.2").data_ptr(), F_,
+                                     bf.hr.data_ptr(), F_, 0, G_SLOPE, bf.gz_scratch.data_ptr(), bf.g_hr.data_ptr(),
+                                     F_, 0, bf.grads["conv3.2.weight"].data_ptr(), bf.grads["conv3.2.bias"].data_ptr(),
+                                     _st()), "conv_out_bwd")
+        # conv3.0
+        self._wgrad(bf, top_in, F_, bf.g_hr, 0, F_, "conv3.0")
+        if self.nup:
+            self._dconv(bf.g_hr, F_, self.wd["conv3.0"], bf.g_up[-1], 0, F_, act=L.ACT_LRELU_MASK, slope=G_SLOPE,
+                        mask=(bf.up[-1], 0))
+        else:
+            self._dconv(bf.g_hr, F_, self.wd["conv3.0"], bf.g_s, 0, F_)
+        # upsampling stages, last to first
+        for u in range(self.nup - 1, -1, -1):
+            hh, ww = h << u, w << u
+            L.check(lib.srb_unshuffle2(bf.g_up[u].data_ptr(), F_, 0, B, hh, ww, F_, bf.g_uns[u].data_ptr(), 4 * F_, 0,
+                                       _st()), "unshuffle")
+            name = f"upsampling.{3 * u}"
+            x_in = bf.feat if u == 0 else bf.up[u - 1]
+            self._wgrad(bf, x_in, F_, bf.g_uns[u], 0, 4 * F_, name, unshuffle=True)
+            if u == 0:
+                self._dconv(bf.g_uns[u], 4 * F_, self.wd[name], bf.g_s, 0, F_)
+            else:
+                self._dconv(bf.g_uns[u], 4 * F_, self.wd[name], bf.g_up[u - 1], 0, F_, act=L.ACT_LRELU_MASK,
+                            slope=G_SLOPE, mask=(bf.up[u - 1], 0))
+        # conv2 (+ the long skip: g_s also flows straight into conv1's output, added in conv_in_bwd)
+        self._wgrad(bf, bf.trunk, F_, bf.g_s, 0, F_, "conv2")
+        self._dconv(bf.g_s, F_, self.wd["conv2"], bf.G[2], 0, F_)
+        # RRDB trunk, last to first
+        for i in range(self.nb - 1, -1, -1):
+            for j in (2, 1, 0):
+                G = bf.G[j]
+                gb = bf.growth[3 * i + j]
+                base = f"res_blocks.{i}.dense_blocks.{j}."
+                s5 = DRB_SCALE * (self.rs if j == 2 else 1.0)
+                sid = self.rs if j == 2 else 1.0
+                for jj in (4, 3, 2, 1):
+                    self._dconv(G, (5 - jj) * F_, self.wd[base + f"slot{jj}"], G, (5 - jj) * F_, F_,
+                                act=L.ACT_LRELU_MASK, slope=G_SLOPE, mask=(gb, jj * F_))
+                if j > 0:
+                    self._dconv(G, 5 * F_, self.wd[base + "slot0"], bf.G[j - 1], 0, F_, res1=(G, 0, sid))
+                elif i > 0:
+                    self._dconv(G, 5 * F_, self.wd[base + "slot0"], bf.G[2], 0, F_, res1=(G, 0, sid),
+                                res2=(bf.G[2], 0, 1.0))
+                else:
+                    self._dconv(G, 5 * F_, self.wd[base + "slot0"], bf.g_out1, 0, F_, res1=(G, 0, sid),
+                                res2=(bf.G[2], 0, 1.0))
+                for k in range(1, 6):
+                    self._wgrad(bf, gb, k * F_, G, (5 - k) * F_ if k < 5 else 0, F_, base + f"b{k}.0",
+                                alpha=s5 if k == 5 else 1.0)
+        # conv1 (models.py:63,122-123): weight gradient from g_out1 + g_s
+        L.check(lib.srb_conv_in_bwd(img.data_ptr(), B, ch, h, w, sv["multiplier"], sv["power"], bf.g_out1.data_ptr(),
+                                    F_, 0, bf.g_s.data_ptr(), F_, 0, F_, bf.grads["conv1.weight"].data_ptr(),
+                                    bf.grads["conv1.bias"].data_ptr(), _st()), "conv_in_bwd")
+        return bf.grads

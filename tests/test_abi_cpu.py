@@ -1,0 +1,68 @@
+"""CPU-side checks: the C-ABI library builds/loads and exports every symbol the binding declares; the drop-in
+modules keep the reference's state_dict layout; the hot path refuses to run without CUDA (no fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from oracle import oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_declared_symbols():
+    from srb200 import _lib as L
+    L.build()
+    lib = L.lib()
+    assert lib.srb_abi_version() == 1
+    hdr = open(os.path.join(ROOT, "include", "srb200.h")).read()
+    declared = set(re.findall(r"\b(srb_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "header declares no entry points?"
+    for name in declared | set(L.exported_symbols()):
+        assert hasattr(lib, name), f"libsrb200.so lacks {name}"
+    assert declared >= set(L.exported_symbols()), \
+        f"binding uses symbols the header does not declare: {set(L.exported_symbols()) - declared}"
+
+
+def test_state_dict_layout_matches_reference_shapes():
+    import models
+    g = models.GeneratorRRDB(1, filters=64, num_res_blocks=2, num_upsample=2, res_scale=0.1)
+    shapes = O.generator_shapes(1, 64, 2, 2)
+    sd = g.state_dict()
+    assert list(sd) == list(shapes)
+    assert all(tuple(sd[k].shape) == tuple(shapes[k]) for k in shapes)
+    d = models.Markovian_Discriminator((1, 80, 80), [16, 32, 32, 64])
+    ds = O.discriminator_shapes()
+    assert list(d.state_dict()) == list(ds) and d.output_shape == (1, 5, 5)
+    assert [n for n, p in g.named_parameters() if not p.requires_grad] == ["power", "multiplier"]
+
+
+def test_default_generator_has_314_entries():
+    import models
+    g = models.GeneratorRRDB(1, filters=64, num_res_blocks=10, num_upsample=2)
+    assert len(g.state_dict()) == 314       # SURVEY.md section 5, checkpoint layout
+
+
+def test_no_cpu_fallback():
+    import models
+    g = models.GeneratorRRDB(1, filters=64, num_res_blocks=1, num_upsample=1)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        g(torch.zeros(1, 1, 8, 8))
+    d = models.Markovian_Discriminator((1, 16, 16), [16])
+    with pytest.raises(RuntimeError, match="CUDA"):
+        d(torch.zeros(1, 1, 16, 16))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        models.SumPool2d(2)(torch.zeros(1, 1, 4, 4))
+
+
+def test_weight_reset_and_uniform_reset_apply():
+    import models
+    g = models.GeneratorRRDB(1, filters=64, num_res_blocks=1, num_upsample=1, uniform_init=True)
+    assert float(g.conv1.bias.abs().sum()) == 0.0
+    before = g.conv2.weight.clone()
+    g.apply(models.weight_reset)
+    assert not torch.equal(before, g.conv2.weight)
+    g.apply(models.uniform_reset)
+    assert float(g.conv3[0].bias.abs().sum()) == 0.0

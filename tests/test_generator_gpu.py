@@ -1,0 +1,130 @@
+"""GPU parity: GeneratorRRDB on the sm_100a kernels vs the CPU oracle and the reference-generated golden vectors.
+Tolerances are the bf16-vs-fp32 ones stated in SURVEY.md section 8c."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+FWD_MAXREL = 3e-2      # max|d| / max|ref|
+FWD_RELL2 = 2e-2
+ENERGY_REL = 5e-3      # per-image energy sum
+GRAD_COS = 0.999
+GRAD_RELL2 = 3e-2
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch.device("cuda:0")
+
+
+def _build(cfg, dev):
+    import models
+    g = models.GeneratorRRDB(1, filters=64, num_res_blocks=cfg["nb"], num_upsample=cfg["nup"], power=cfg["power"],
+                             multiplier=cfg["multiplier"], res_scale=cfg["res_scale"])
+    sd = O.make_generator_sd(cfg["seed"], num_res_blocks=cfg["nb"], num_upsample=cfg["nup"], power=cfg["power"],
+                             multiplier=cfg["multiplier"], gain=cfg["gain"])
+    g.load_state_dict(sd, strict=True)
+    g.thres = cfg["thres"]
+    g.train(cfg["training"])
+    return g.to(dev), sd
+
+
+def _close(got, ref, maxrel=FWD_MAXREL, rell2=FWD_RELL2):
+    got, ref = got.float().cpu(), ref.float().cpu()
+    scale = ref.abs().max().item() + 1e-12
+    assert (got - ref).abs().max().item() / scale <= maxrel, ((got - ref).abs().max().item(), scale)
+    assert (got - ref).norm().item() / (ref.norm().item() + 1e-12) <= rell2
+
+
+@pytest.mark.parametrize("name", ["g_fwd_train_x4", "g_fwd_eval_x4", "g_fwd_eval_pow_x2", "g_fwd_train_pow_x2",
+                                  "g_fwd_nb2_x8"])
+def test_forward_matches_golden(golden, name):
+    dev = _dev()
+    case = golden[name]
+    cfg = case["cfg"]
+    g, _ = _build(cfg, dev)
+    hr, lr = O.synthetic_jets(cfg["batch"], cfg["lr_size"] * 2 ** cfg["nup"], 2 ** cfg["nup"], cfg["seed"] + 7)
+    with torch.no_grad():
+        out = g(lr.to(dev))
+    thr = cfg["thres"]
+    ref, ref_srs = case["out"], case["srs"]
+    if thr > 0:
+        # hardshrink is discontinuous at the threshold: compare away from it
+        near = (ref.abs() - thr).abs() < 0.05 * thr + 1e-3
+        near |= (out.cpu().abs() - thr).abs() < 0.05 * thr + 1e-3
+        o, r = out.cpu().clone(), ref.clone()
+        o[near] = 0; r[near] = 0
+        _close(o, r)
+    else:
+        _close(out, ref)
+        _close(g.srs, ref_srs)
+    e_ref = ref.sum((1, 2, 3)); e = out.cpu().sum((1, 2, 3))
+    assert ((e - e_ref).abs() / e_ref.abs().clamp_min(1e-3)).max().item() <= (ENERGY_REL if thr == 0 else 5e-2)
+
+
+def test_training_grads_match_golden_and_oracle(golden):
+    dev = _dev()
+    case = golden["g_train_x4"]
+    cfg = case["cfg"]
+    g, sd = _build(cfg, dev)
+    hr, lr = O.synthetic_jets(cfg["batch"], cfg["lr_size"] * 4, 4, cfg["seed"] + 7)
+    out = g(lr.to(dev))
+    loss = F.l1_loss(out, hr.to(dev))
+    loss.backward()
+    assert abs(loss.item() - case["loss"]) <= 2e-2 * abs(case["loss"])
+    # oracle gradients (full tensors) on the CPU
+    sdr = {k: (v.clone().requires_grad_(True) if k not in ("power", "multiplier") else v) for k, v in sd.items()}
+    o_ref, _ = O.generator_forward(sdr, lr, res_scale=cfg["res_scale"], thres=cfg["thres"], training=True)
+    F.l1_loss(o_ref, hr).backward()
+    worst = (1.0, "")
+    for n, p in g.named_parameters():
+        if not p.requires_grad:
+            continue
+        assert p.grad is not None, n
+        a, b = p.grad.float().cpu().reshape(-1), sdr[n].grad.reshape(-1)
+        cos = torch.dot(a, b).item() / (a.norm().item() * b.norm().item() + 1e-30)
+        rel = (a - b).norm().item() / (b.norm().item() + 1e-30)
+        worst = min(worst, (cos, n))
+        assert cos >= GRAD_COS, (n, cos, rel)
+        assert rel <= 5e-2, (n, cos, rel)
+        h = case["grads"][n]["head"]
+        assert (a[:64] - h).abs().max().item() <= 5e-2 * (h.abs().max().item() + b.abs().max().item() * 0.05 + 1e-12)
+
+
+@pytest.mark.parametrize("batch,lr_size,nup,nb", [(3, 20, 2, 1), (130, 20, 2, 1), (5, 13, 1, 2)])
+def test_forward_backward_vs_oracle_shapes(batch, lr_size, nup, nb):
+    """covers MT=1 and MT=2 tile paths, odd widths, and a second RRDB (outer skip in backward)."""
+    dev = _dev()
+    cfg = dict(nb=nb, nup=nup, power=1.0, multiplier=1.0, res_scale=0.1, seed=31, gain=1.2, thres=0.0, training=True)
+    g, sd = _build(cfg, dev)
+    hr, lr = O.synthetic_jets(batch, lr_size * 2 ** nup, 2 ** nup, 77)
+    out = g(lr.to(dev))
+    (out * out).mean().backward()
+    sdr = {k: (v.clone().requires_grad_(True) if k not in ("power", "multiplier") else v) for k, v in sd.items()}
+    o_ref, _ = O.generator_forward(sdr, lr, res_scale=0.1, thres=0.0, training=True)
+    (o_ref * o_ref).mean().backward()
+    _close(out.detach(), o_ref.detach())
+    for n, p in g.named_parameters():
+        if p.requires_grad:
+            a, b = p.grad.float().cpu().reshape(-1), sdr[n].grad.reshape(-1)
+            cos = torch.dot(a, b).item() / (a.norm().item() * b.norm().item() + 1e-30)
+            assert cos >= GRAD_COS, (n, cos)
+
+
+def test_tcgen05_matches_naive_kernels_bitwise_close():
+    """same bf16 data path, fp32 accumulation order differs only: results agree to bf16 rounding."""
+    dev = _dev()
+    from srb200 import _lib as L
+    cfg = dict(nb=1, nup=2, power=1.0, multiplier=1.0, res_scale=0.1, seed=5, gain=1.0, thres=0.0, training=False)
+    g, _ = _build(cfg, dev)
+    _, lr = O.synthetic_jets(4, 80, 4, 9)
+    with torch.no_grad():
+        a = g(lr.to(dev)).clone()
+        g._engine().impl = L.IMPL_NAIVE
+        b = g(lr.to(dev)).clone()
+        g._engine().impl = L.IMPL_TCGEN05
+    assert (a - b).abs().max().item() <= 2e-2 * b.abs().max().item()
