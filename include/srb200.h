@@ -150,6 +150,24 @@ int srb_lrelu_bwd(const float* g, const float* ref, float* gx, long long n, floa
 int srb_sumpool_fwd(const float* x, float* y, int BC, int H, int W, int k, void* stream);
 int srb_sumpool_bwd(const float* gy, float* gx, int BC, int H, int W, int k, void* stream);
 
+/* ---- losses and optimizer (csrc/optim_loss.cu) ---------------------------------------------------
+ * srb_adam_step   : torch.optim.Adam (esrgan.py:299,305,555,624) over one flat fp32 buffer; `state` = device
+ *                   float[2] {step, skip}; the update is skipped unless *gate_value > gate_threshold (the
+ *                   d_threshold test of esrgan.py:623 without a host sync); gate_value may be NULL.
+ * srb_pixel_losses: esrgan.py:471,487,490  L1(batch-mean image) and L1(SumPool(gen), lr) + gradient w.r.t. gen.
+ * srb_ragan       : esrgan.py:507-508 (u=fake, v=real) and 578-588 (u=real, v=fake): loss, dL/du, dL/dv.
+ * srb_gp_fwd/bwd  : esrgan.py:604-605 gradient-penalty reduction and its gradient.                           */
+int srb_adam_step(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2, float eps,
+                  float weight_decay, float grad_scale, float* state, const float* gate_value, float gate_threshold,
+                  void* stream);
+int srb_pixel_losses(const float* gen, const float* gt, const float* lr, int B, int H, int W, int k, float w_hr,
+                     float w_lr, int accumulate, float* msign, float* dsign, float* acc, float* grad, void* stream);
+int srb_ragan(const float* u, const float* v, int B, int n, float eps, float* loss, float* gu, float* gv,
+              void* stream);
+int srb_gp_fwd(const float* g, int B, int n, float coef, float* norms, float* loss, void* stream);
+int srb_gp_bwd(const float* g, const float* norms, int B, int n, float coef, const float* gloss, float* gg,
+               void* stream);
+
 /* Bring-up microbenchmark: sustained tcgen05.mma issue rate (csrc/probe.cu); not on the product path. */
 int srb_probe_mma_rate(int cta_group, int N, int iters, int a_row_shift, int mn_major, int b_lbo, int n_ctas,
                        long long* cycles_out, void* stream);

@@ -64,9 +64,9 @@ class ResidualInResidualDenseBlock(nn.Module):
 
 class _GeneratorFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, gen, x, *params):
+    def forward(ctx, gen, need, x, *params):
+        # grad mode is always off inside Function.forward, so the caller decides whether to keep activations
         ctx.gen = gen
-        need = torch.is_grad_enabled() and any(p.requires_grad for p in params)
         out, srs = gen._engine().forward(x, power=gen._host_scalar("power"), multiplier=gen._host_scalar("multiplier"),
                                          thres=float(gen.thres), training=gen.training, save_for_backward=need)
         ctx.n = len(params)
@@ -80,7 +80,7 @@ class _GeneratorFn(torch.autograd.Function):
         for name, p in gen.named_parameters():
             g = grads.get(name) if p.requires_grad else None
             res.append(g)
-        return (None, None) + tuple(res)
+        return (None, None, None) + tuple(res)
 
 
 class GeneratorRRDB(nn.Module):
@@ -158,7 +158,9 @@ class GeneratorRRDB(nn.Module):
         if not self._native:
             raise RuntimeError("CUDA srb200: use_transposed_conv / fully_tconv_upsample / num_final_layer_res / "
                                "drop_rate variants are constructor-surface only in this build (SURVEY.md 8f-4)")
-        out, srs = _GeneratorFn.apply(self, x, *self.parameters())
+        params = list(self.parameters())
+        need = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        out, srs = _GeneratorFn.apply(self, need, x, *params)
         self.srs = srs
         return out
 

@@ -151,18 +151,22 @@ class LReLUBwd(torch.autograd.Function):
         return LReLUBwd.apply(gg, ref, ctx.slope), None, None
 
 
-def conv2d(x, conv: nn.Conv2d):
+def conv2d(x, conv: nn.Conv2d, detach_params: bool = False):
     if conv.kernel_size != (3, 3) or conv.padding != (1, 1) or conv.stride[0] != conv.stride[1] \
             or conv.stride[0] not in (1, 2):
         raise RuntimeError("CUDA srb200: discriminator kernels cover 3x3 / padding 1 / stride 1 or 2")
-    return ConvFwd.apply(x, conv.weight, conv.bias, conv.stride[0])
+    w, b = conv.weight, conv.bias
+    if detach_params:
+        w, b = w.detach(), (b.detach() if b is not None else None)
+    return ConvFwd.apply(x, w, b, conv.stride[0])
 
 
-def sequential_forward(seq: nn.Sequential, x):
-    """Run an nn.Sequential of Conv2d / LeakyReLU (the discriminator_block pattern, models.py:140-146)."""
+def sequential_forward(seq: nn.Sequential, x, detach_params: bool = False):
+    """Run an nn.Sequential of Conv2d / LeakyReLU (the discriminator_block pattern, models.py:140-146).
+    ``detach_params`` treats the weights as constants (the generator step only needs d/d input)."""
     for m in seq:
         if isinstance(m, nn.Conv2d):
-            x = conv2d(x, m)
+            x = conv2d(x, m, detach_params)
         elif isinstance(m, nn.LeakyReLU):
             x = LReLU.apply(x, m.negative_slope)
         else:

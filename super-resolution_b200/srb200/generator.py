@@ -52,6 +52,7 @@ class GeneratorEngine:
         self._pack_key = None
         self._packs_bwd_ready = False
         self._saved = None
+        self.grad_views = None       # optional name -> fp32 view: where backward writes parameter gradients
         self.names3x3 = self._conv_names()
 
     # ------------------------------------------------------------------ parameter bookkeeping
@@ -266,6 +267,8 @@ class GeneratorEngine:
         if sv["key"] != self._params_key():
             raise RuntimeError("CUDA srb200: parameters changed between forward and backward")
         bf, img = sv["bf"], sv["img"]
+        if self.grad_views is not None:
+            bf.grads = self.grad_views
         B, ch, h, w = img.shape
         F_, lib = self.F, L.lib()
         H, W = h << self.nup, w << self.nup

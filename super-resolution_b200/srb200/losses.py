@@ -1,0 +1,91 @@
+"""Loss reductions of the GAN step on the C ABI kernels (esrgan.py:471-508, 578-606)."""
+from __future__ import annotations
+
+import torch
+
+from . import _lib as L
+
+EPS = 1e-7   # esrgan.py:319
+
+
+def _st() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _c(t):
+    return t.detach().contiguous().float()
+
+
+class PixelLossWork:
+    """Scratch for srb_pixel_losses for one (B, H, W, factor)."""
+
+    def __init__(self, B, H, W, k, dev):
+        self.B, self.H, self.W, self.k = B, H, W, k
+        self.msign = torch.empty(H * W, device=dev)
+        self.dsign = torch.empty(B * (H // k) * (W // k), device=dev)
+        self.acc = torch.zeros(2, device=dev)
+
+
+def pixel_losses(gen, gt, lr, k, w_hr, w_lr, grad_out, accumulate, work: PixelLossWork):
+    """loss_hr = L1(mean_b gen, mean_b gt) (esrgan.py:487); loss_lr = L1(SumPool_k(gen), lr) (471,490).
+    Adds w_hr * d loss_hr/d gen + w_lr * d loss_lr/d gen into ``grad_out`` (or overwrites it).
+    Returns (loss_hr, loss_lr) as 0-dim device tensors."""
+    gen, gt, lr = _c(gen), _c(gt), _c(lr)
+    B, Cc, H, W = gen.shape
+    assert Cc == 1, "pixel loss kernel is single-channel (jet images)"
+    L.check(L.lib().srb_pixel_losses(gen.data_ptr(), gt.data_ptr(), lr.data_ptr(), B, H, W, k, float(w_hr),
+                                     float(w_lr), int(accumulate), work.msign.data_ptr(), work.dsign.data_ptr(),
+                                     work.acc.data_ptr(), grad_out.data_ptr() if grad_out is not None else None,
+                                     _st()), "pixel_losses")
+    acc = work.acc.clone()
+    return acc[0] / (H * W), acc[1] / (B * (H // k) * (W // k))
+
+
+class RaGAN(torch.autograd.Function):
+    """0.5*[BCE(eps + u - mean_b v, 1) + BCE(eps + v - mean_b u, 0)]  (esrgan.py:507-508 with u=fake, v=real;
+    esrgan.py:578-588 with u=real, v=fake).  Loss and both gradients come out of one kernel."""
+
+    @staticmethod
+    def forward(ctx, u, v):
+        uc, vc = _c(u), _c(v)
+        B = uc.shape[0]
+        n = uc.numel() // B
+        loss = torch.empty((), device=u.device)
+        gu, gv = torch.empty_like(uc), torch.empty_like(vc)
+        L.check(L.lib().srb_ragan(uc.data_ptr(), vc.data_ptr(), B, n, EPS, loss.data_ptr(), gu.data_ptr(),
+                                  gv.data_ptr(), _st()), "ragan")
+        ctx.save_for_backward(gu, gv)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        gu, gv = ctx.saved_tensors
+        return (g * gu if ctx.needs_input_grad[0] else None), (g * gv if ctx.needs_input_grad[1] else None)
+
+
+class GradientPenalty(torch.autograd.Function):
+    """((||g_b||_2 - 1)^2).mean() * coef   (esrgan.py:604-605 with coef = lambda_reg / 2)."""
+
+    @staticmethod
+    def forward(ctx, g, coef):
+        gc = _c(g)
+        B = gc.shape[0]
+        n = gc.numel() // B
+        norms = torch.empty(B, device=g.device)
+        loss = torch.zeros((), device=g.device)
+        L.check(L.lib().srb_gp_fwd(gc.data_ptr(), B, n, float(coef), norms.data_ptr(), loss.data_ptr(), _st()),
+                "gp_fwd")
+        ctx.save_for_backward(gc, norms)
+        ctx.coef = coef
+        return loss
+
+    @staticmethod
+    def backward(ctx, gl):
+        gc, norms = ctx.saved_tensors
+        B = gc.shape[0]
+        n = gc.numel() // B
+        gg = torch.empty_like(gc)
+        glc = gl.detach().float().contiguous()
+        L.check(L.lib().srb_gp_bwd(gc.data_ptr(), norms.data_ptr(), B, n, float(ctx.coef), glc.data_ptr(),
+                                   gg.data_ptr(), _st()), "gp_bwd")
+        return gg, None
