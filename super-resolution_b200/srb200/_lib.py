@@ -152,7 +152,11 @@ def lib():
     return _lib
 
 
+CALLS = [0]       # successful C-ABI launches (every entry point launches >= 1 kernel); bench.py reports the delta
+
+
 def check(status: int, what: str = "") -> None:
+    CALLS[0] += 1
     if status != 0:
         msg = lib().srb_last_error().decode("utf-8", "replace")
         raise RuntimeError(f"{msg} [{what}]" if what else msg)

@@ -11,6 +11,27 @@ from . import _lib as L
 Tensor = torch.Tensor
 
 
+PROFILE = None    # when set to a list, conv3x3 / wgrad3x3 append (kind, algorithmic_flops, start_event, end_event)
+
+
+class _Prof:
+    def __init__(self, kind, flops):
+        self.kind, self.flops = kind, flops
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if PROFILE is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            PROFILE.append((self.kind, self.flops, self.e0, e1))
+        return False
+
+
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
@@ -97,7 +118,8 @@ def conv3x3(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Tensor]
     if res2 is not None:
         a.res2, a.res2_cstride, a.res2_coff, a.res2_scale = res2[0].data_ptr(), res2[0].shape[-1], res2[1], res2[2]
     a.impl, a.flags = impl, flags
-    L.check(L.lib().srb_conv3x3(C.byref(a), _stream()), "conv3x3")
+    with _Prof("conv3x3", 2.0 * B * a.H * a.W * 9 * cin * cout):
+        L.check(L.lib().srb_conv3x3(C.byref(a), _stream()), "conv3x3")
 
 
 def wgrad_workspace_bytes(batch: int, H: int, W: int, cin: int, cout: int) -> int:
@@ -124,7 +146,8 @@ def wgrad3x3(x: Tensor, x_coff: int, cin: int, gy: Tensor, gy_coff: int, cout: i
             workspace = torch.empty(need, dtype=torch.uint8, device=x.device)
         a.workspace, a.workspace_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
     a.impl, a.flags = impl, flags
-    L.check(L.lib().srb_wgrad3x3(C.byref(a), _stream()), "wgrad3x3")
+    with _Prof("wgrad3x3", 2.0 * B * a.H * a.W * 9 * cin * cout):
+        L.check(L.lib().srb_wgrad3x3(C.byref(a), _stream()), "wgrad3x3")
 
 
 def read_fault() -> int:
