@@ -140,7 +140,8 @@ int srb_unshuffle2(const void* src, int s_cstride, int s_coff, int B, int H, int
  *   penalty of esrgan.py:598-606 differentiates the input gradient again).
  * srb_lrelu_fwd/bwd: nn.LeakyReLU(0.2) (models.py:143,145).   srb_sumpool_fwd/bwd: SumPool2d (models.py:297-305). */
 int srb_dconv_fwd(const float* x, const float* w, const float* bias, float* y, int B, int Cin, int H, int W, int Cout,
-                  int stride, void* stream);
+                  int stride, int act, float slope, void* stream);   /* act != 0: LeakyReLU(slope) fused */
+int srb_set_dconv_impl(int impl);   /* 0: register-tiled kernels (default); 1: simple cross-check kernels */
 int srb_dconv_dgrad(const float* gy, const float* w, float* gx, int B, int Cin, int H, int W, int Cout, int stride,
                     void* stream);
 int srb_dconv_wgrad(const float* gy, const float* x, float* dw, float* db, int B, int Cin, int H, int W, int Cout,

@@ -172,19 +172,39 @@ using namespace srb;
     if (e_ != cudaSuccess) return set_cuda_error(name " launch", e_);  \
   } while (0)
 
+namespace srb {
+int dconv_fwd_fast(const float* x, const float* w, const float* bias, float* y, int B, int Cin, int H, int W, int Cout,
+                   int stride, int act, float slope, cudaStream_t st);
+int dconv_dgrad_fast(const float* gy, const float* w, float* gx, int B, int Cin, int H, int W, int Cout, int stride,
+                     cudaStream_t st);
+int dconv_wgrad_fast(const float* gy, const float* x, float* dw, float* db, int B, int Cin, int H, int W, int Cout,
+                     int stride, cudaStream_t st);
+static int g_dconv_impl = 0;     // 0: register-tiled kernels (disc_fast.cu); 1: the simple kernels above (cross-check)
+}  // namespace srb
+extern "C" int srb_set_dconv_impl(int impl) { srb::g_dconv_impl = impl; return 0; }
+
 extern "C" int srb_dconv_fwd(const float* x, const float* w, const float* bias, float* y, int B, int Cin, int H, int W,
-                             int Cout, int stride, void* stream) {
+                             int Cout, int stride, int act, float slope, void* stream) {
+  if (stride != 1 && stride != 2) return set_error("dconv: stride must be 1 or 2");
+  if (g_dconv_impl == 0) return dconv_fwd_fast(x, w, bias, y, B, Cin, H, W, Cout, stride, act, slope, (cudaStream_t)stream);
   const int Ho = (H - 1) / stride + 1, Wo = (W - 1) / stride + 1;
   constexpr int OCB = 8;
   dim3 grid(ceil_div(Ho * Wo, 128), ceil_div(Cout, OCB), B);
   const size_t smem = sizeof(float) * OCB * Cin * 9;
   dconv_fwd_kernel<OCB><<<grid, 128, smem, (cudaStream_t)stream>>>(x, w, bias, y, B, Cin, H, W, Cout, stride, Ho, Wo);
   SRB_CHECK_LAUNCH("dconv_fwd");
+  if (act) {
+    const long long n = 1LL * B * Cout * Ho * Wo;
+    lrelu_fwd_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(y, y, n, slope);
+    SRB_CHECK_LAUNCH("lrelu_fwd");
+  }
   return 0;
 }
 
 extern "C" int srb_dconv_dgrad(const float* gy, const float* w, float* gx, int B, int Cin, int H, int W, int Cout,
                                int stride, void* stream) {
+  if (stride != 1 && stride != 2) return set_error("dconv: stride must be 1 or 2");
+  if (g_dconv_impl == 0) return dconv_dgrad_fast(gy, w, gx, B, Cin, H, W, Cout, stride, (cudaStream_t)stream);
   const int Ho = (H - 1) / stride + 1, Wo = (W - 1) / stride + 1;
   constexpr int ICB = 8;
   dim3 grid(ceil_div(H * W, 128), ceil_div(Cin, ICB), B);
@@ -196,6 +216,8 @@ extern "C" int srb_dconv_dgrad(const float* gy, const float* w, float* gx, int B
 
 extern "C" int srb_dconv_wgrad(const float* gy, const float* x, float* dw, float* db, int B, int Cin, int H, int W,
                                int Cout, int stride, void* stream) {
+  if (stride != 1 && stride != 2) return set_error("dconv: stride must be 1 or 2");
+  if (g_dconv_impl == 0) return dconv_wgrad_fast(gy, x, dw, db, B, Cin, H, W, Cout, stride, (cudaStream_t)stream);
   const int Ho = (H - 1) / stride + 1, Wo = (W - 1) / stride + 1;
   cudaMemsetAsync(dw, 0, sizeof(float) * Cout * Cin * 9, (cudaStream_t)stream);
   if (db) cudaMemsetAsync(db, 0, sizeof(float) * Cout, (cudaStream_t)stream);

@@ -241,7 +241,8 @@ int wgrad3x3_tc_launch(const srb_wgrad3x3_args* a, cudaStream_t stream) {
   if (e != cudaSuccess) return set_cuda_error("wgrad_reduce launch", e);
   if (a->dbias) {
     if (!a->accumulate) cudaMemsetAsync(a->dbias, 0, sizeof(float) * a->cout, stream);
-    int slices = int(R / 2048); if (slices < 1) slices = 1; if (slices > 64) slices = 64;
+    int slices = int(R / 256); if (slices < 1) slices = 1;
+    const int max_slices = 4 * sm_count() / (a->cout / 64); if (slices > max_slices) slices = max_slices;
     dim3 g(a->cout / 64, slices);
     colsum_kernel<<<g, 256, 0, stream>>>((const __nv_bfloat16*)a->gy, (int)R, a->gy_cstride, a->gy_coff, a->cout,
                                          a->alpha, a->accumulate, a->unshuffle, a->dbias);

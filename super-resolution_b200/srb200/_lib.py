@@ -106,7 +106,8 @@ _SIGS = {
     "srb_unshuffle2": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                  C.c_int, C.c_int, C.c_void_p]),
     "srb_dconv_fwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
-                                C.c_int, C.c_int, C.c_void_p]),
+                                C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]),
+    "srb_set_dconv_impl": (C.c_int, [C.c_int]),
     "srb_dconv_dgrad": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                   C.c_int, C.c_void_p]),
     "srb_dconv_wgrad": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,

@@ -25,13 +25,15 @@ def _f32(t):
     return t.detach().contiguous().float()
 
 
-def _raw_fwd(x, w, b, stride):
+def _raw_fwd(x, w, b, stride, slope=None):
+    """conv (+ bias) (+ LeakyReLU(slope) fused in the kernel epilogue when slope is given)"""
     B, Cin, H, W = x.shape
     Cout = w.shape[0]
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     y = torch.empty(B, Cout, Ho, Wo, device=x.device)
     L.check(L.lib().srb_dconv_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None, y.data_ptr(),
-                                  B, Cin, H, W, Cout, stride, _st()), "dconv_fwd")
+                                  B, Cin, H, W, Cout, stride, int(slope is not None),
+                                  float(slope) if slope is not None else 0.0, _st()), "dconv_fwd")
     return y
 
 
@@ -115,6 +117,29 @@ class ConvWgrad(torch.autograd.Function):
         return g_gy, g_x, None, None, None
 
 
+class ConvLReLU(torch.autograd.Function):
+    """y = LeakyReLU(conv3x3(x, w) + b), one kernel (discriminator_block, models.py:142-145).  Backward is composed of
+    the differentiable pieces LReLUBwd / ConvDgrad / ConvWgrad, so it can itself be differentiated."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, stride, slope):
+        _need_cuda(x)
+        y = _raw_fwd(_f32(x), _f32(w), _f32(b) if b is not None else None, stride, slope)
+        ctx.save_for_backward(x, w, y)
+        ctx.stride, ctx.has_b, ctx.slope = stride, b is not None, slope
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w, y = ctx.saved_tensors
+        gz = LReLUBwd.apply(gy, y, ctx.slope)
+        gx = ConvDgrad.apply(gz, w, x.shape, ctx.stride) if ctx.needs_input_grad[0] else None
+        gw = gb = None
+        if ctx.needs_input_grad[1] or (ctx.has_b and ctx.needs_input_grad[2]):
+            gw, gb = ConvWgrad.apply(gz, x, w.shape, ctx.stride, ctx.has_b)
+        return gx, gw, (gb if ctx.has_b else None), None, None
+
+
 class LReLU(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, slope):
@@ -151,24 +176,83 @@ class LReLUBwd(torch.autograd.Function):
         return LReLUBwd.apply(gg, ref, ctx.slope), None, None
 
 
-def conv2d(x, conv: nn.Conv2d, detach_params: bool = False):
+def _check_conv(conv: nn.Conv2d):
     if conv.kernel_size != (3, 3) or conv.padding != (1, 1) or conv.stride[0] != conv.stride[1] \
             or conv.stride[0] not in (1, 2):
         raise RuntimeError("CUDA srb200: discriminator kernels cover 3x3 / padding 1 / stride 1 or 2")
+
+
+def conv2d(x, conv: nn.Conv2d, detach_params: bool = False, slope=None):
+    _check_conv(conv)
     w, b = conv.weight, conv.bias
     if detach_params:
         w, b = w.detach(), (b.detach() if b is not None else None)
+    if slope is not None:
+        return ConvLReLU.apply(x, w, b, conv.stride[0], slope)
     return ConvFwd.apply(x, w, b, conv.stride[0])
 
 
+def _layers(seq: nn.Sequential):
+    """[(conv, slope-or-None)] for a Conv2d / LeakyReLU chain; None if the Sequential holds anything else."""
+    mods, out, i = list(seq), [], 0
+    while i < len(mods):
+        m = mods[i]
+        if not isinstance(m, nn.Conv2d):
+            return None
+        slope = None
+        if i + 1 < len(mods) and isinstance(mods[i + 1], nn.LeakyReLU):
+            slope = mods[i + 1].negative_slope
+            i += 1
+        out.append((m, slope))
+        i += 1
+    return out
+
+
 def sequential_forward(seq: nn.Sequential, x, detach_params: bool = False):
-    """Run an nn.Sequential of Conv2d / LeakyReLU (the discriminator_block pattern, models.py:140-146).
-    ``detach_params`` treats the weights as constants (the generator step only needs d/d input)."""
-    for m in seq:
-        if isinstance(m, nn.Conv2d):
-            x = conv2d(x, m, detach_params)
-        elif isinstance(m, nn.LeakyReLU):
-            x = LReLU.apply(x, m.negative_slope)
-        else:
-            x = m(x)
+    """Run an nn.Sequential of Conv2d / LeakyReLU (the discriminator_block pattern, models.py:140-146); each
+    conv + LeakyReLU pair is one fused kernel.  ``detach_params`` treats the weights as constants (the generator
+    step only needs d/d input)."""
+    layers = _layers(seq)
+    if layers is None:
+        for m in seq:
+            if isinstance(m, nn.Conv2d):
+                x = conv2d(x, m, detach_params)
+            elif isinstance(m, nn.LeakyReLU):
+                x = LReLU.apply(x, m.negative_slope)
+            else:
+                x = m(x)
+        return x
+    for conv, slope in layers:
+        x = conv2d(x, conv, detach_params, slope)
     return x
+
+
+def input_gradient(seq: nn.Sequential, x):
+    """d sum(D(x)) / d x as a function that is differentiable w.r.t. the weights: what
+    autograd.grad(D(x), x, ones, create_graph=True) returns at esrgan.py:602, built explicitly from the input-gradient
+    kernels so that no weight gradient is computed (and thrown away) on the way.  Returns (pred, grad_x)."""
+    layers = _layers(seq)
+    if layers is None:
+        raise RuntimeError("CUDA srb200: input_gradient expects a Conv2d / LeakyReLU chain")
+    acts, h = [], _f32(x)
+    with torch.no_grad():
+        for conv, slope in layers:
+            _check_conv(conv)
+            acts.append(h)
+            h = _raw_fwd(h, _f32(conv.weight), _f32(conv.bias) if conv.bias is not None else None, conv.stride[0],
+                         slope)
+            acts.append(h)
+    pred = h
+    g = torch.ones_like(pred)
+    for n in range(len(layers) - 1, -1, -1):
+        conv, slope = layers[n]
+        xin, y = acts[2 * n], acts[2 * n + 1]
+        if slope is not None:
+            g = LReLUBwd.apply(g, y, slope)
+        g = ConvDgrad.apply(g, conv.weight, xin.shape, conv.stride[0])
+    return pred, g
+
+
+def set_impl(simple: bool) -> None:
+    """Switch the discriminator convolutions to the simple cross-check kernels (tests) or back."""
+    L.check(L.lib().srb_set_dconv_impl(1 if simple else 0), "set_dconv_impl")

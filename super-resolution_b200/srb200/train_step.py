@@ -116,9 +116,8 @@ class GANTrainStep:
             loss_D = LS.RaGAN.apply(pred_real, pred_fake)                                  # esrgan.py:578-588
             if self.l_reg > 0:
                 eps = epsilons[k].to(dev) if epsilons is not None else torch.rand(B, 1, 1, 1, device=dev)   # 598
-                interp = (eps * real + (1 - eps) * fake).requires_grad_(True)              # 599-600
-                pred_i = D.sequential_forward(d.model, interp)                             # 601
-                (gi,) = torch.autograd.grad(pred_i, interp, torch.ones_like(pred_i), create_graph=True)   # 602
+                interp = eps * real + (1 - eps) * fake                                     # 599-600
+                _, gi = D.input_gradient(d.model, interp)                                  # 601-602
                 gp = LS.GradientPenalty.apply(gi.reshape(B, -1), self.l_reg / 2)           # 604-605
                 loss_D = loss_D + gp                                                       # 606
                 out_losses[f"gp{k}"] = gp.detach()
