@@ -151,6 +151,33 @@ int srb_lrelu_bwd(const float* g, const float* ref, float* gx, long long n, floa
 int srb_sumpool_fwd(const float* x, float* y, int BC, int H, int W, int k, void* stream);
 int srb_sumpool_bwd(const float* gy, float* gx, int BC, int H, int W, int k, void* stream);
 
+/* ---- discriminator stack on warp-level bf16 tensor-core MMA (csrc/disc_mma.cu) ---------------------
+ * Activations bf16 NHWC [B][H][W][C] (C in {16,32,64}), images / predictions fp32 [B][H][W].  The hand-scheduled
+ * discriminator engine (srb200/disc_engine.py) composes these into the forward of models.py:140-174 and into the
+ * first and second derivatives the training step needs (esrgan.py:493-508, 569-616).
+ * srb_dmma_conv : nn.Conv2d(k=3, p=1, stride 1|2) + bias + LeakyReLU(0.2) (models.py:142-145,168); with the
+ *                 "dgrad" weight packs also the input gradient (stride 1: flipped conv; stride 2: transposed form,
+ *                 `transposed` = 1, source = gradient map at half resolution).  act: 0 none, 1 LeakyReLU(slope),
+ *                 2 multiply by LeakyReLU'(ref) (ref = stored activation with the geometry of the output).
+ *                 Exactly one of in_bf16 / in_f32 (single channel) is given; out_f32 only for cout == 1.
+ * srb_dmma_wgrad: filter/bias gradient, ACCUMULATED into dw [cout][cin][3][3] / db [cout] with atomics.
+ * srb_dl1_*     : the Cin = 1 image end (first conv of models.py:142) in fp32 on CUDA cores: forward (optionally
+ *                 with the mask epilogue), input gradient (fp32 image out), filter/bias gradient (accumulated).
+ * srb_dpack     : fp32 OIHW parameters (offsets into one flat buffer) -> zero-padded bf16 [9][rows][k] packs;
+ *                 kind 0 forward, 1 stride-1 input gradient (flipped, transposed), 2 stride-2 input gradient. */
+int srb_dmma_conv(const void* in_bf16, const float* in_f32, int cin, const void* w_packed, const float* bias, int cout,
+                  void* out_bf16, float* out_f32, const void* ref, int B, int Hs, int Ws, int Hd, int Wd, int stride,
+                  int transposed, int act, float slope, void* stream);
+int srb_dmma_wgrad(const void* gz_bf16, const float* gz_f32, int cout, const void* a_bf16, int cin, float* dw,
+                   float* db, int B, int Hi, int Wi, int Ho, int Wo, int stride, void* stream);
+int srb_dl1_fwd(const float* img, const float* w, const float* bias, void* out_bf16, const void* ref, int C, int B,
+                int H, int W, int act, float slope, void* stream);
+int srb_dl1_dgrad(const void* gz_bf16, const float* w, float* gx, int C, int B, int H, int W, void* stream);
+int srb_dl1_wgrad(const void* gz_bf16, const float* img, float* dw, float* db, int C, int B, int H, int W,
+                  void* stream);
+int srb_dpack(const float* flat_params, void* dst_bf16, int n_items, const long long* src_off,
+              const long long* dst_off, const int* cout, const int* cin, const int* kind, void* stream);
+
 /* ---- losses and optimizer (csrc/optim_loss.cu) ---------------------------------------------------
  * srb_adam_step   : torch.optim.Adam (esrgan.py:299,305,555,624) over one flat fp32 buffer; `state` = device
  *                   float[2] {step, skip}; the update is skipped unless *gate_value > gate_threshold (the

@@ -1,0 +1,732 @@
+// K5 (tensor-core path): the discriminator's small-channel 3x3 convolutions (models.py:140-146,168) and both
+// halves of their backward on warp-level bf16 MMA (mma.sync m16n8k16, fp32 accumulate).
+//
+// Why not tcgen05 here: the layers are 16/32/64 channels wide on 80x80 ... 5x5 maps (23 MMAC per image for the whole
+// stack); they are bound by HBM traffic and launch count, not by the tensor pipe, and the UMMA tile (128 x N x 16 from
+// 128B-swizzled smem) would be mostly padding.  The warp-level MMA lets one fragment be ANY 16 output pixels: rows of
+// an ldmatrix are per-lane shared-memory addresses, so 3x3 taps, stride 2, the four phases of the stride-2 input
+// gradient and image borders are all just address arithmetic on a zero-padded shared-memory tile.
+//
+// Layout: activations bf16 NHWC [B][H][W][C] (C in {16,32,64}; no padding in global memory), images fp32 [B][H][W].
+//   dmma_conv_kernel<KS,NT,MODE>   MODE 0: y = epi(conv_s(x, w) + b)       (forward, stride 1|2; also the stride-1
+//                                          input gradient when given the flipped/transposed weight pack)
+//                                  MODE 1: stride-2 input gradient (transposed conv) by output phase
+//                                  epi: bias, LeakyReLU, or multiply by LeakyReLU'(ref) (the mask of the layer below)
+//   dmma_wgrad_kernel<KS,MT>       dW[co][ci][t] += sum_pixels gz[p][co] * a[p*s + t][ci];  db[co] += sum gz
+//   dl1_* kernels                  the 1-channel image end of the stack (Cin = 1) on CUDA cores in fp32
+#include "common.cuh"
+
+namespace srb {
+
+__device__ __forceinline__ uint32_t dsmem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x2(uint32_t addr, uint32_t& r0, uint32_t& r1) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+               "{%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t dpack_bf16(float a, float b) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ float dbf_lo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float dbf_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+
+struct DmmaConvP {
+  const __nv_bfloat16* in;     // bf16 NHWC source [B][Hs][Ws][cin]          (or in_f32 for a 1-channel fp32 source)
+  const float* in_f32;
+  const __nv_bfloat16* w;      // bf16 [9][NT*8][KS*16], zero padded
+  const float* bias;           // fp32 [cout] or null
+  __nv_bfloat16* out;          // bf16 NHWC [B][Hd][Wd][cout] or null
+  float* out_f32;              // fp32 [B][Hd][Wd] (cout == 1) or null
+  const __nv_bfloat16* ref;    // act == 2: mask reference, geometry of out
+  int B, Hs, Ws, Hd, Wd;       // source / destination maps
+  int cin, cout;               // real channel counts (<= KS*16, <= NT*8)
+  int stride;                  // MODE 0
+  int TH, IMGS;                // tile = IMGS images x TH rows (MODE 0: destination rows; MODE 1: phase-grid rows)
+  int tiles_y, n_tiles;
+  int act;                     // 0 none, 1 LeakyReLU(slope), 2 multiply by (ref > 0 ? 1 : slope)
+  float slope;
+};
+
+constexpr int kDmmaThreads = 256;
+
+template <int KS, int NT, int MODE>
+__global__ void __launch_bounds__(kDmmaThreads)
+dmma_conv_kernel(const DmmaConvP p) {
+  constexpr int PP = KS * 32 + 16;                    // bytes per pixel row in shared memory (16 B skew: conflict-free ldmatrix)
+  constexpr int NROWS = NT * 8;
+  extern __shared__ __align__(16) uint8_t dsm[];
+  uint8_t* w_s = dsm;
+  uint8_t* in_s = dsm + 9 * NROWS * PP;
+  const int S = MODE == 0 ? p.stride : 1;
+  const int Wg = MODE == 0 ? p.Wd : p.Wd / 2;         // width of the fragment grid (destination or phase grid)
+  const int Hg = MODE == 0 ? p.Hd : p.Hd / 2;
+  const int TR = MODE == 0 ? p.TH * S + 2 : p.TH + 1;
+  const int TC = MODE == 0 ? Wg * S + 2 : Wg + 1;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // weights -> shared memory (once per CTA)
+  {
+    constexpr int CH = KS * 2;                        // 16-byte chunks per row
+    const uint4* src = reinterpret_cast<const uint4*>(p.w);
+    for (int i = threadIdx.x; i < 9 * NROWS * CH; i += kDmmaThreads) {
+      const int row = i / CH, c = i - row * CH;
+      *reinterpret_cast<uint4*>(w_s + row * PP + c * 16) = __ldg(src + i);
+    }
+  }
+  const int M_img = p.TH * Wg;
+  const int M = p.IMGS * M_img;                       // fragment rows per tile (per phase for MODE 1)
+  const int nfrag = (M + 15) >> 4;
+  const int npair = (nfrag + 1) >> 1;
+  constexpr int NPH = MODE == 0 ? 1 : 4;
+
+  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+    const int ty = tile % p.tiles_y;
+    const int img0 = (tile / p.tiles_y) * p.IMGS;
+    const int y0 = ty * p.TH;                         // first fragment-grid row of the tile
+    __syncthreads();                                  // previous tile fully consumed (and weights visible)
+    // ---- stage the zero-padded source tile
+    {
+      constexpr int CH = KS * 2;
+      const int total = p.IMGS * TR * TC * CH;
+      const int gy0 = MODE == 0 ? y0 * S - 1 : y0;
+      const int gx0 = MODE == 0 ? -1 : 0;
+      for (int i = threadIdx.x; i < total; i += kDmmaThreads) {
+        const int c = i % CH;
+        int r = i / CH;
+        const int tc = r % TC; r /= TC;
+        const int tr = r % TR;
+        const int im = r / TR;
+        const int gy = gy0 + tr, gx = gx0 + tc, b = img0 + im;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (b < p.B && gy >= 0 && gy < p.Hs && gx >= 0 && gx < p.Ws) {
+          const size_t pix = (static_cast<size_t>(b) * p.Hs + gy) * p.Ws + gx;
+          if (p.in_f32) {
+            if (c == 0) v.x = dpack_bf16(__ldg(p.in_f32 + pix), 0.f);
+          } else if (c * 8 < p.cin) {
+            v = __ldg(reinterpret_cast<const uint4*>(p.in + pix * p.cin) + c);
+          }
+        }
+        *reinterpret_cast<uint4*>(in_s + ((im * TR + tr) * TC + tc) * PP + c * 16) = v;
+      }
+    }
+    __syncthreads();
+
+    for (int it = warp; it < NPH * npair; it += kDmmaThreads / 32) {
+      const int ph = MODE == 0 ? 0 : it / npair;
+      const int pr = MODE == 0 ? it : it - ph * npair;
+      const int py = ph >> 1, px = ph & 1;
+      float acc[2][NT][4];
+#pragma unroll
+      for (int f = 0; f < 2; ++f)
+#pragma unroll
+        for (int n = 0; n < NT; ++n)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) acc[f][n][i] = 0.f;
+      // per-lane ldmatrix row base for the two fragments
+      uint32_t abase[2];
+#pragma unroll
+      for (int f = 0; f < 2; ++f) {
+        int m = (pr * 2 + f) * 16 + (lane & 15);
+        if (m >= M) m = 0;
+        const int im = m / M_img;
+        const int rem = m - im * M_img;
+        const int yl = rem / Wg, x = rem - yl * Wg;
+        abase[f] = dsmem_u32(in_s) + ((im * TR + yl * S) * TC + x * S) * PP + (lane >> 4) * 16;
+      }
+      const bool two = (pr * 2 + 1) < nfrag;
+      const uint32_t wlane = dsmem_u32(w_s) + ((lane & 7) + ((lane >> 4) << 3)) * PP + ((lane >> 3) & 1) * 16;
+      const uint32_t wlane2 = dsmem_u32(w_s) + (lane & 7) * PP + ((lane >> 3) & 1) * 16;   // x2 form (NT == 1)
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        if (MODE == 1 && ((ky ^ py) & 1) == 0) continue;        // needs ky == py + 1 (mod 2)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          if (MODE == 1 && ((kx ^ px) & 1) == 0) continue;
+          int toff;
+          if (MODE == 0) toff = (ky * TC + kx) * PP;
+          else toff = (((py == 1 && ky == 0) ? TC : 0) + ((px == 1 && kx == 0) ? 1 : 0)) * PP;
+          const int wt = (ky * 3 + kx) * NROWS * PP;
+#pragma unroll
+          for (int kk = 0; kk < KS; ++kk) {
+            uint32_t a0[4], a1[4];
+            ldsm_x4(abase[0] + toff + kk * 32, a0);
+            if (two) ldsm_x4(abase[1] + toff + kk * 32, a1);
+            if (NT == 1) {
+              uint32_t b0, b1;
+              ldsm_x2(wlane2 + wt + kk * 32, b0, b1);
+              mma_bf16_16816(acc[0][0], a0, b0, b1);
+              if (two) mma_bf16_16816(acc[1][0], a1, b0, b1);
+            } else {
+#pragma unroll
+              for (int np = 0; np < NT / 2; ++np) {
+                uint32_t b[4];
+                ldsm_x4(wlane + wt + np * 16 * PP + kk * 32, b);
+                mma_bf16_16816(acc[0][2 * np], a0, b[0], b[1]);
+                mma_bf16_16816(acc[0][2 * np + 1], a0, b[2], b[3]);
+                if (two) {
+                  mma_bf16_16816(acc[1][2 * np], a1, b[0], b[1]);
+                  mma_bf16_16816(acc[1][2 * np + 1], a1, b[2], b[3]);
+                }
+              }
+            }
+          }
+        }
+      }
+      // ---- epilogue: rows g and g+8 of each fragment, columns nt*8 + 2t, +1
+      const int g = lane >> 2, t2 = (lane & 3) * 2;
+#pragma unroll
+      for (int f = 0; f < 2; ++f) {
+        if (f == 1 && !two) break;
+#pragma unroll
+        for (int hrow = 0; hrow < 2; ++hrow) {
+          const int m = (pr * 2 + f) * 16 + g + hrow * 8;
+          if (m >= M) continue;
+          const int im = m / M_img;
+          const int rem = m - im * M_img;
+          const int yl = rem / Wg, x = rem - yl * Wg;
+          const int b = img0 + im, yg = y0 + yl;
+          if (b >= p.B || yg >= Hg) continue;
+          const int yd = MODE == 0 ? yg : 2 * yg + py;
+          const int xd = MODE == 0 ? x : 2 * x + px;
+          const size_t pix = (static_cast<size_t>(b) * p.Hd + yd) * p.Wd + xd;
+#pragma unroll
+          for (int n = 0; n < NT; ++n) {
+            const int col = n * 8 + t2;
+            if (col >= p.cout) continue;
+            float v0 = acc[f][n][hrow * 2], v1 = acc[f][n][hrow * 2 + 1];
+            if (p.bias) {
+              v0 += __ldg(p.bias + col);
+              if (col + 1 < p.cout) v1 += __ldg(p.bias + col + 1);
+            }
+            if (p.act == 1) {
+              v0 = v0 > 0.f ? v0 : v0 * p.slope;
+              v1 = v1 > 0.f ? v1 : v1 * p.slope;
+            } else if (p.act == 2) {
+              if (p.cout == 1) {
+                v0 *= __bfloat162float(p.ref[pix]) > 0.f ? 1.f : p.slope;
+              } else {
+                const uint32_t r = __ldg(reinterpret_cast<const uint32_t*>(p.ref + pix * p.cout + col));
+                v0 *= dbf_lo(r) > 0.f ? 1.f : p.slope;
+                v1 *= dbf_hi(r) > 0.f ? 1.f : p.slope;
+              }
+            }
+            if (p.cout == 1) {
+              if (p.out_f32) p.out_f32[pix] = v0;
+              if (p.out) p.out[pix] = __float2bfloat16(v0);
+            } else {
+              *reinterpret_cast<uint32_t*>(p.out + pix * p.cout + col) = dpack_bf16(v0, v1);
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- weight gradient
+struct DmmaWgradP {
+  const __nv_bfloat16* gz;     // bf16 NHWC [B][Ho][Wo][cout]   (or gz_f32 for a 1-channel fp32 gradient)
+  const float* gz_f32;
+  const __nv_bfloat16* a;      // bf16 NHWC [B][Hi][Wi][cin]
+  float* dw;                   // fp32 [cout][cin][3][3], accumulated with atomics
+  float* db;                   // fp32 [cout] or null
+  int B, Hi, Wi, Ho, Wo, cin, cout, stride;
+  int co_off;                  // first output channel handled by this launch (MT*16 channels from there)
+  int TH, IMGS, tiles_y, n_tiles;
+};
+
+constexpr int kDwgThreads = 288;   // nine warps: one per filter tap
+
+template <int KS, int MT>
+__global__ void __launch_bounds__(kDwgThreads)
+dmma_wgrad_kernel(const DmmaWgradP p) {
+  constexpr int PPA = KS * 32 + 16;
+  constexpr int PPG = MT * 32 + 16;
+  constexpr int NT = KS * 2;
+  extern __shared__ __align__(16) uint8_t dsm[];
+  const int S = p.stride;
+  const int TR = p.TH * S + 2, TC = p.Wo * S + 2;
+  const int M_img = p.TH * p.Wo;
+  const int M = p.IMGS * M_img;
+  const int M16 = (M + 15) & ~15;
+  uint8_t* a_s = dsm;
+  uint8_t* g_s = dsm + p.IMGS * TR * TC * PPA;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ky = warp / 3, kx = warp - ky * 3;
+
+  float acc[MT][NT][4];
+#pragma unroll
+  for (int m = 0; m < MT; ++m)
+#pragma unroll
+    for (int n = 0; n < NT; ++n)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[m][n][i] = 0.f;
+  float dbacc = 0.f;
+
+  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+    const int ty = tile % p.tiles_y;
+    const int img0 = (tile / p.tiles_y) * p.IMGS;
+    const int y0 = ty * p.TH;
+    __syncthreads();
+    {  // input tile with halo
+      constexpr int CH = KS * 2;
+      const int total = p.IMGS * TR * TC * CH;
+      for (int i = threadIdx.x; i < total; i += kDwgThreads) {
+        const int c = i % CH;
+        int r = i / CH;
+        const int tc = r % TC; r /= TC;
+        const int tr = r % TR;
+        const int im = r / TR;
+        const int gy = y0 * S - 1 + tr, gx = tc - 1, b = img0 + im;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (b < p.B && gy >= 0 && gy < p.Hi && gx >= 0 && gx < p.Wi && c * 8 < p.cin)
+          v = __ldg(reinterpret_cast<const uint4*>(p.a + ((static_cast<size_t>(b) * p.Hi + gy) * p.Wi + gx) * p.cin) + c);
+        *reinterpret_cast<uint4*>(a_s + ((im * TR + tr) * TC + tc) * PPA + c * 16) = v;
+      }
+    }
+    {  // gradient tile, rows = fragment-row index m (zero beyond the valid pixels)
+      constexpr int CH = MT * 2;
+      for (int i = threadIdx.x; i < M16 * CH; i += kDwgThreads) {
+        const int c = i % CH, m = i / CH;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (m < M) {
+          const int im = m / M_img;
+          const int rem = m - im * M_img;
+          const int yl = rem / p.Wo, x = rem - yl * p.Wo;
+          const int b = img0 + im, y = y0 + yl;
+          if (b < p.B && y < p.Ho) {
+            const size_t pix = (static_cast<size_t>(b) * p.Ho + y) * p.Wo + x;
+            if (p.gz_f32) {
+              if (c == 0) v.x = dpack_bf16(__ldg(p.gz_f32 + pix), 0.f);
+            } else if (p.co_off + c * 8 < p.cout) {
+              v = __ldg(reinterpret_cast<const uint4*>(p.gz + pix * p.cout + p.co_off) + c);
+            }
+          }
+        }
+        *reinterpret_cast<uint4*>(g_s + m * PPG + c * 16) = v;
+      }
+    }
+    __syncthreads();
+    if (p.db && threadIdx.x < MT * 16) {
+      float s = 0.f;
+      for (int m = 0; m < M; ++m) s += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(g_s + m * PPG + threadIdx.x * 2));
+      dbacc += s;
+    }
+    const int kA = (lane & 7) + ((lane >> 4) << 3);
+    const int kB = (lane & 7) + (((lane >> 3) & 1) << 3);
+    for (int ch = 0; ch < M16 / 16; ++ch) {
+      int m = ch * 16 + kB;
+      if (m >= M) m = 0;                                  // gradient row is zero there: any finite input row will do
+      const int im = m / M_img;
+      const int rem = m - im * M_img;
+      const int yl = rem / p.Wo, x = rem - yl * p.Wo;
+      const uint32_t baddr = dsmem_u32(a_s) + ((im * TR + yl * S + ky) * TC + x * S + kx) * PPA + (lane >> 4) * 16;
+      const uint32_t aaddr = dsmem_u32(g_s) + (ch * 16 + kA) * PPG + ((lane >> 3) & 1) * 16;
+      uint32_t af[MT][4];
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) ldsm_x4_t(aaddr + mt * 32, af[mt]);
+#pragma unroll
+      for (int np = 0; np < KS; ++np) {
+        uint32_t b[4];
+        ldsm_x4_t(baddr + np * 32, b);
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+          mma_bf16_16816(acc[mt][2 * np], af[mt], b[0], b[1]);
+          mma_bf16_16816(acc[mt][2 * np + 1], af[mt], b[2], b[3]);
+        }
+      }
+    }
+  }
+  // ---- flush: dw[co][ci][tap]
+  const int g = lane >> 2, t2 = (lane & 3) * 2;
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int n = 0; n < NT; ++n)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int co = p.co_off + mt * 16 + g + (i >> 1) * 8;
+        const int ci = n * 8 + t2 + (i & 1);
+        if (co < p.cout && ci < p.cin) atomicAdd(p.dw + (static_cast<size_t>(co) * p.cin + ci) * 9 + warp, acc[mt][n][i]);
+      }
+  if (p.db && threadIdx.x < MT * 16 && p.co_off + threadIdx.x < p.cout) atomicAdd(p.db + p.co_off + threadIdx.x, dbacc);
+}
+
+// ---------------------------------------------------------------------------------------------- image end (Cin = 1)
+// y[b][p][c] = epi(bias[c] + sum_t w[c][t] * img[b][p + t]);  one thread per pixel, all C channels (C <= 64, C % 8 == 0)
+template <int C>
+__global__ void __launch_bounds__(256)
+dl1_fwd_kernel(const float* __restrict__ img, const float* __restrict__ w, const float* __restrict__ bias,
+               __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ ref, int B, int H, int W, int act,
+               float slope) {
+  __shared__ float ws[9][C];
+  __shared__ float bs[C];
+  for (int i = threadIdx.x; i < 9 * C; i += blockDim.x) ws[i % 9][i / 9] = w[i];     // w is [C][1][3][3]
+  for (int i = threadIdx.x; i < C; i += blockDim.x) bs[i] = bias ? bias[i] : 0.f;
+  __syncthreads();
+  const long long total = 1LL * B * H * W;
+  for (long long pix = blockIdx.x * (long long)blockDim.x + threadIdx.x; pix < total; pix += (long long)gridDim.x * blockDim.x) {
+    const int x = int(pix % W);
+    const int y = int((pix / W) % H);
+    const float* ip = img + pix;
+    float v[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
+      v[t] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(ip + (t / 3 - 1) * W + (t % 3 - 1)) : 0.f;
+    }
+    uint4* op = reinterpret_cast<uint4*>(out + pix * C);
+    const uint4* rp = reinterpret_cast<const uint4*>(ref + pix * C);
+#pragma unroll
+    for (int c8 = 0; c8 < C / 8; ++c8) {
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float s = bs[c8 * 8 + j];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) s += v[t] * ws[t][c8 * 8 + j];
+        o[j] = s;
+      }
+      if (act == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = o[j] > 0.f ? o[j] : o[j] * slope;
+      } else if (act == 2) {
+        const uint4 r = __ldg(rp + c8);
+        const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          o[2 * j] *= dbf_lo(rw[j]) > 0.f ? 1.f : slope;
+          o[2 * j + 1] *= dbf_hi(rw[j]) > 0.f ? 1.f : slope;
+        }
+      }
+      uint4 ov;
+      ov.x = dpack_bf16(o[0], o[1]); ov.y = dpack_bf16(o[2], o[3]); ov.z = dpack_bf16(o[4], o[5]); ov.w = dpack_bf16(o[6], o[7]);
+      op[c8] = ov;
+    }
+  }
+}
+
+// gx[b][p] = sum_t sum_c gz[b][p - t][c] * w[c][t]   (fp32 image gradient out)
+template <int C>
+__global__ void __launch_bounds__(256)
+dl1_dgrad_kernel(const __nv_bfloat16* __restrict__ gz, const float* __restrict__ w, float* __restrict__ gx, int B,
+                 int H, int W) {
+  __shared__ float ws[9][C];
+  for (int i = threadIdx.x; i < 9 * C; i += blockDim.x) ws[i % 9][i / 9] = w[i];
+  __syncthreads();
+  const long long total = 1LL * B * H * W;
+  for (long long pix = blockIdx.x * (long long)blockDim.x + threadIdx.x; pix < total; pix += (long long)gridDim.x * blockDim.x) {
+    const int x = int(pix % W);
+    const int y = int((pix / W) % H);
+    float s = 0.f;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      // output pixel q = p - (t - center) contributed w[t] * img[p] to y[q]  ->  gx[p] += gz[q] * w[t]
+      const int yy = y - (t / 3 - 1), xx = x - (t % 3 - 1);
+      if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
+      const uint4* gp = reinterpret_cast<const uint4*>(gz + (pix - (t / 3 - 1) * W - (t % 3 - 1)) * C);
+#pragma unroll
+      for (int c8 = 0; c8 < C / 8; ++c8) {
+        const uint4 r = __ldg(gp + c8);
+        const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) s += dbf_lo(rw[j]) * ws[t][c8 * 8 + 2 * j] + dbf_hi(rw[j]) * ws[t][c8 * 8 + 2 * j + 1];
+      }
+    }
+    gx[pix] = s;
+  }
+}
+
+// dw[c][t] += sum_p gz[p][c] * img[p + t];  db[c] += sum_p gz[p][c].   Block = one image band; thread = (c, t) pair
+// (+ C extra threads for the bias), both operands staged in shared memory.
+template <int C>
+__global__ void __launch_bounds__(C * 10)
+dl1_wgrad_kernel(const __nv_bfloat16* __restrict__ gz, const float* __restrict__ img, float* __restrict__ dw,
+                 float* __restrict__ db, int B, int H, int W, int TH) {
+  extern __shared__ __align__(16) uint8_t dsm[];
+  const int TR = TH + 2, TC = W + 2;
+  float* im_s = reinterpret_cast<float*>(dsm);                          // [TR][TC]
+  __nv_bfloat16* g_s = reinterpret_cast<__nv_bfloat16*>(im_s + ((TR * TC + 3) & ~3));          // [TH*W][C]
+  const int bands = (H + TH - 1) / TH;
+  const int c = threadIdx.x % C, t = threadIdx.x / C;                   // t == 9: bias thread
+  const int dy = t / 3, dx = t % 3;
+  float acc = 0.f;
+  for (int item = blockIdx.x; item < B * bands; item += gridDim.x) {
+    const int b = item / bands, y0 = (item % bands) * TH;
+    const int rows = min(TH, H - y0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < TR * TC; i += blockDim.x) {
+      const int r = i / TC, cc = i % TC;
+      const int gy = y0 - 1 + r, gxx = cc - 1;
+      im_s[i] = (gy >= 0 && gy < H && gxx >= 0 && gxx < W) ? __ldg(img + (static_cast<size_t>(b) * H + gy) * W + gxx) : 0.f;
+    }
+    const uint4* src = reinterpret_cast<const uint4*>(gz + (static_cast<size_t>(b) * H + y0) * W * C);
+    for (int i = threadIdx.x; i < rows * W * C / 8; i += blockDim.x) reinterpret_cast<uint4*>(g_s)[i] = __ldg(src + i);
+    __syncthreads();
+    if (t < 9) {
+      for (int r = 0; r < rows; ++r) {
+        const float* ip = im_s + (r + dy) * TC + dx;
+        const __nv_bfloat16* gp = g_s + r * W * C + c;
+        for (int x = 0; x < W; ++x) acc += __bfloat162float(gp[x * C]) * ip[x];
+      }
+    } else {
+      for (int i = 0; i < rows * W; ++i) acc += __bfloat162float(g_s[i * C + c]);
+    }
+  }
+  if (t < 9) atomicAdd(dw + c * 9 + t, acc);
+  else if (db) atomicAdd(db + c, acc);
+}
+
+// ---------------------------------------------------------------------------------------------- weight packs
+// One launch packs every layer of a discriminator: fp32 OIHW (flat parameter buffer) -> bf16 [9][rows][kpad].
+//   kind 0 (forward, and MODE 1 input gradient of stride-2 layers uses kind 2):  wp[t][co][ci] = w[co][ci][t]
+//   kind 1 (stride-1 input gradient as a forward conv over gz):                  wp[t][ci][co] = w[co][ci][8 - t]
+//   kind 2 (stride-2 input gradient, transposed form):                           wp[t][ci][co] = w[co][ci][t]
+struct DPackItem { long long src_off; long long dst_off; int cout, cin, rows, kpad, kind; };
+struct DPackTable { int n; DPackItem it[24]; };
+
+__global__ void dpack_kernel(const float* __restrict__ flat, __nv_bfloat16* __restrict__ dst, const DPackTable tab) {
+  const DPackItem e = tab.it[blockIdx.y];
+  const int total = 9 * e.rows * e.kpad;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int k = i % e.kpad;
+    const int r = (i / e.kpad) % e.rows;
+    const int t = i / (e.kpad * e.rows);
+    float v = 0.f;
+    if (e.kind == 0) {
+      if (r < e.cout && k < e.cin) v = flat[e.src_off + (static_cast<long long>(r) * e.cin + k) * 9 + t];
+    } else {
+      const int tt = e.kind == 1 ? 8 - t : t;
+      if (r < e.cin && k < e.cout) v = flat[e.src_off + (static_cast<long long>(k) * e.cin + r) * 9 + tt];
+    }
+    dst[e.dst_off + i] = __float2bfloat16(v);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- host side
+static int pad16(int c) { return (c + 15) & ~15; }
+static int pad8(int c) { return (c + 7) & ~7; }
+
+static void dmma_tile_plan(int Hg, int Wg, int B, size_t bytes_per_src_pixel_row /*unused*/, int* TH, int* IMGS) {
+  const int target = 192;
+  if (Hg * Wg >= 128) {
+    int th = (target + Wg - 1) / Wg;
+    if (th > Hg) th = Hg;
+    const int nt = (Hg + th - 1) / th;
+    th = (Hg + nt - 1) / nt;
+    *TH = th; *IMGS = 1;
+  } else {
+    int n = (target + Hg * Wg - 1) / (Hg * Wg);
+    if (n > B) n = B;
+    if (n < 1) n = 1;
+    *TH = Hg; *IMGS = n;
+  }
+}
+
+template <int KS, int NT, int MODE>
+static int dmma_conv_launch_t(DmmaConvP& p, cudaStream_t st) {
+  constexpr int PP = KS * 32 + 16;
+  const int S = MODE == 0 ? p.stride : 1;
+  const int Wg = MODE == 0 ? p.Wd : p.Wd / 2, Hg = MODE == 0 ? p.Hd : p.Hd / 2;
+  int TH, IMGS;
+  dmma_tile_plan(Hg, Wg, p.B, 0, &TH, &IMGS);
+  size_t smem;
+  for (;;) {
+    const int TR = MODE == 0 ? TH * S + 2 : TH + 1, TC = MODE == 0 ? Wg * S + 2 : Wg + 1;
+    smem = size_t(9) * NT * 8 * PP + size_t(IMGS) * TR * TC * PP;
+    if (smem <= 200 * 1024) break;
+    if (IMGS > 1) --IMGS; else if (TH > 1) TH = (TH + 1) / 2; else return set_error("dmma_conv: tile does not fit in shared memory");
+  }
+  p.TH = TH; p.IMGS = IMGS;
+  p.tiles_y = (Hg + TH - 1) / TH;
+  p.n_tiles = p.tiles_y * ((p.B + IMGS - 1) / IMGS);
+  static bool attr = false;
+  if (!attr) { cudaFuncSetAttribute(dmma_conv_kernel<KS, NT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
+  int per_sm = int((220 * 1024) / (smem + 1024)); if (per_sm < 1) per_sm = 1; if (per_sm > 4) per_sm = 4;
+  int grid = sm_count() * per_sm; if (grid > p.n_tiles) grid = p.n_tiles;
+  dmma_conv_kernel<KS, NT, MODE><<<grid, kDmmaThreads, smem, st>>>(p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error("dmma_conv launch", e);
+  return 0;
+}
+
+template <int KS, int MODE>
+static int dmma_conv_launch_n(DmmaConvP& p, cudaStream_t st) {
+  const int nt = pad8(p.cout) / 8;
+  switch (nt) {
+    case 1: return dmma_conv_launch_t<KS, 1, MODE>(p, st);
+    case 2: return dmma_conv_launch_t<KS, 2, MODE>(p, st);
+    case 4: return dmma_conv_launch_t<KS, 4, MODE>(p, st);
+    case 8: return dmma_conv_launch_t<KS, 8, MODE>(p, st);
+  }
+  return set_error("dmma_conv: output channels must be 1, 16, 32 or 64");
+}
+
+template <int KS, int MT>
+static int dmma_wgrad_launch_t(DmmaWgradP& p, cudaStream_t st) {
+  constexpr int PPA = KS * 32 + 16, PPG = MT * 32 + 16;
+  int TH, IMGS;
+  dmma_tile_plan(p.Ho, p.Wo, p.B, 0, &TH, &IMGS);
+  size_t smem;
+  for (;;) {
+    const int TR = TH * p.stride + 2, TC = p.Wo * p.stride + 2;
+    const int M16 = (IMGS * TH * p.Wo + 15) & ~15;
+    smem = size_t(IMGS) * TR * TC * PPA + size_t(M16) * PPG;
+    if (smem <= 200 * 1024) break;
+    if (IMGS > 1) --IMGS; else if (TH > 1) TH = (TH + 1) / 2; else return set_error("dmma_wgrad: tile does not fit in shared memory");
+  }
+  p.TH = TH; p.IMGS = IMGS;
+  p.tiles_y = (p.Ho + TH - 1) / TH;
+  p.n_tiles = p.tiles_y * ((p.B + IMGS - 1) / IMGS);
+  static bool attr = false;
+  if (!attr) { cudaFuncSetAttribute(dmma_wgrad_kernel<KS, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
+  int per_sm = int((220 * 1024) / (smem + 1024)); if (per_sm < 1) per_sm = 1; if (per_sm > 3) per_sm = 3;
+  int grid = sm_count() * per_sm; if (grid > p.n_tiles) grid = p.n_tiles;
+  dmma_wgrad_kernel<KS, MT><<<grid, kDwgThreads, smem, st>>>(p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error("dmma_wgrad launch", e);
+  return 0;
+}
+
+}  // namespace srb
+
+using namespace srb;
+
+extern "C" int srb_dmma_conv(const void* in_bf16, const float* in_f32, int cin, const void* w_packed, const float* bias,
+                             int cout, void* out_bf16, float* out_f32, const void* ref, int B, int Hs, int Ws, int Hd,
+                             int Wd, int stride, int transposed, int act, float slope, void* stream) {
+  if ((!in_bf16 && !in_f32) || !w_packed || (!out_bf16 && !out_f32)) return set_error("dmma_conv: null pointer");
+  if (in_f32 && cin != 1) return set_error("dmma_conv: fp32 source must be single-channel");
+  if (!in_f32 && cin != 16 && cin != 32 && cin != 64) return set_error("dmma_conv: input channels must be 16, 32 or 64");
+  if (cout != 1 && cout != 16 && cout != 32 && cout != 64) return set_error("dmma_conv: output channels must be 1, 16, 32 or 64");
+  if (cout != 1 && !out_bf16) return set_error("dmma_conv: bf16 output required");
+  if (act == 2 && !ref) return set_error("dmma_conv: mask epilogue without reference");
+  if (transposed && ((Hd & 1) || (Wd & 1) || Hs * 2 != Hd || Ws * 2 != Wd)) return set_error("dmma_conv: transposed form needs even maps");
+  if (!transposed && (stride < 1 || stride > 2 || (Hs - 1) / stride + 1 != Hd || (Ws - 1) / stride + 1 != Wd))
+    return set_error("dmma_conv: geometry mismatch");
+  DmmaConvP p{};
+  p.in = (const __nv_bfloat16*)in_bf16; p.in_f32 = in_f32; p.w = (const __nv_bfloat16*)w_packed; p.bias = bias;
+  p.out = (__nv_bfloat16*)out_bf16; p.out_f32 = out_f32; p.ref = (const __nv_bfloat16*)ref;
+  p.B = B; p.Hs = Hs; p.Ws = Ws; p.Hd = Hd; p.Wd = Wd; p.cin = cin; p.cout = cout; p.stride = stride;
+  p.act = act; p.slope = slope;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int ks = pad16(cin) / 16;
+  if (transposed) {
+    switch (ks) {
+      case 1: return dmma_conv_launch_n<1, 1>(p, st);
+      case 2: return dmma_conv_launch_n<2, 1>(p, st);
+      case 4: return dmma_conv_launch_n<4, 1>(p, st);
+    }
+  } else {
+    switch (ks) {
+      case 1: return dmma_conv_launch_n<1, 0>(p, st);
+      case 2: return dmma_conv_launch_n<2, 0>(p, st);
+      case 4: return dmma_conv_launch_n<4, 0>(p, st);
+    }
+  }
+  return set_error("dmma_conv: unsupported channel count");
+}
+
+extern "C" int srb_dmma_wgrad(const void* gz_bf16, const float* gz_f32, int cout, const void* a_bf16, int cin, float* dw,
+                              float* db, int B, int Hi, int Wi, int Ho, int Wo, int stride, void* stream) {
+  if ((!gz_bf16 && !gz_f32) || !a_bf16 || !dw) return set_error("dmma_wgrad: null pointer");
+  if (gz_f32 && cout != 1) return set_error("dmma_wgrad: fp32 gradient must be single-channel");
+  if (cin != 16 && cin != 32 && cin != 64) return set_error("dmma_wgrad: input channels must be 16, 32 or 64");
+  if (cout != 1 && cout != 16 && cout != 32 && cout != 64) return set_error("dmma_wgrad: output channels must be 1, 16, 32 or 64");
+  if (stride < 1 || stride > 2 || (Hi - 1) / stride + 1 != Ho || (Wi - 1) / stride + 1 != Wo) return set_error("dmma_wgrad: geometry mismatch");
+  DmmaWgradP p{};
+  p.gz = (const __nv_bfloat16*)gz_bf16; p.gz_f32 = gz_f32; p.a = (const __nv_bfloat16*)a_bf16; p.dw = dw; p.db = db;
+  p.B = B; p.Hi = Hi; p.Wi = Wi; p.Ho = Ho; p.Wo = Wo; p.cin = cin; p.cout = cout; p.stride = stride;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int ks = cin / 16, mt = pad16(cout) / 16;
+#define SRB_WG(K, M) if (ks == K && mt == M) return dmma_wgrad_launch_t<K, M>(p, st);
+  SRB_WG(1, 1) SRB_WG(1, 2) SRB_WG(1, 4) SRB_WG(2, 1) SRB_WG(2, 2) SRB_WG(2, 4) SRB_WG(4, 1) SRB_WG(4, 2)
+#undef SRB_WG
+  if (ks == 4 && mt == 4) {      // 64 x 64: two passes of 32 output channels (keeps the accumulators in registers)
+    if (dmma_wgrad_launch_t<4, 2>(p, st)) return 1;
+    p.co_off = 32;
+    return dmma_wgrad_launch_t<4, 2>(p, st);
+  }
+  return set_error("dmma_wgrad: unsupported channel count");
+}
+
+extern "C" int srb_dl1_fwd(const float* img, const float* w, const float* bias, void* out_bf16, const void* ref, int C,
+                           int B, int H, int W, int act, float slope, void* stream) {
+  if (!img || !w || !out_bf16) return set_error("dl1_fwd: null pointer");
+  if (act == 2 && !ref) return set_error("dl1_fwd: mask epilogue without reference");
+  const long long total = 1LL * B * H * W;
+  int grid = ceil_div(total, 256); if (grid > sm_count() * 8) grid = sm_count() * 8;
+  cudaStream_t st = (cudaStream_t)stream;
+#define SRB_L1(CC) if (C == CC) dl1_fwd_kernel<CC><<<grid, 256, 0, st>>>(img, w, bias, (__nv_bfloat16*)out_bf16, (const __nv_bfloat16*)ref, B, H, W, act, slope);
+  SRB_L1(16) else SRB_L1(32) else SRB_L1(64) else return set_error("dl1_fwd: channels must be 16, 32 or 64");
+#undef SRB_L1
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error("dl1_fwd launch", e);
+  return 0;
+}
+
+extern "C" int srb_dl1_dgrad(const void* gz_bf16, const float* w, float* gx, int C, int B, int H, int W, void* stream) {
+  if (!gz_bf16 || !w || !gx) return set_error("dl1_dgrad: null pointer");
+  const long long total = 1LL * B * H * W;
+  int grid = ceil_div(total, 256); if (grid > sm_count() * 8) grid = sm_count() * 8;
+  cudaStream_t st = (cudaStream_t)stream;
+#define SRB_L1(CC) if (C == CC) dl1_dgrad_kernel<CC><<<grid, 256, 0, st>>>((const __nv_bfloat16*)gz_bf16, w, gx, B, H, W);
+  SRB_L1(16) else SRB_L1(32) else SRB_L1(64) else return set_error("dl1_dgrad: channels must be 16, 32 or 64");
+#undef SRB_L1
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error("dl1_dgrad launch", e);
+  return 0;
+}
+
+extern "C" int srb_dl1_wgrad(const void* gz_bf16, const float* img, float* dw, float* db, int C, int B, int H, int W,
+                             void* stream) {
+  if (!gz_bf16 || !img || !dw) return set_error("dl1_wgrad: null pointer");
+  int TH = 8; if (TH > H) TH = H;
+  while (TH > 1 && size_t(TH + 2) * (W + 2) * 4 + 16 + size_t(TH) * W * C * 2 > 96 * 1024) TH = (TH + 1) / 2;
+  const size_t smem = size_t(TH + 2) * (W + 2) * 4 + 16 + size_t(TH) * W * C * 2;
+  const int bands = (H + TH - 1) / TH;
+  int grid = B * bands; if (grid > sm_count() * 4) grid = sm_count() * 4;
+  cudaStream_t st = (cudaStream_t)stream;
+#define SRB_L1(CC) if (C == CC) { \
+    static bool attr = false; \
+    if (!attr) { cudaFuncSetAttribute(dl1_wgrad_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); attr = true; } \
+    dl1_wgrad_kernel<CC><<<grid, CC * 10, smem, st>>>((const __nv_bfloat16*)gz_bf16, img, dw, db, B, H, W, TH); }
+  SRB_L1(16) else SRB_L1(32) else SRB_L1(64) else return set_error("dl1_wgrad: channels must be 16, 32 or 64");
+#undef SRB_L1
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error("dl1_wgrad launch", e);
+  return 0;
+}
+
+extern "C" int srb_dpack(const float* flat_params, void* dst_bf16, int n_items, const long long* src_off,
+                         const long long* dst_off, const int* cout, const int* cin, const int* kind, void* stream) {
+  if (!flat_params || !dst_bf16 || n_items < 1 || n_items > 24) return set_error("dpack: bad arguments");
+  DPackTable tab{};
+  tab.n = n_items;
+  for (int i = 0; i < n_items; ++i) {
+    DPackItem& e = tab.it[i];
+    e.src_off = src_off[i]; e.dst_off = dst_off[i]; e.cout = cout[i]; e.cin = cin[i]; e.kind = kind[i];
+    if (kind[i] == 0) { e.rows = pad8(cout[i]); e.kpad = pad16(cin[i]); }
+    else { e.rows = pad8(cin[i]); e.kpad = pad16(cout[i]); }
+  }
+  dim3 grid(8, n_items);
+  dpack_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(flat_params, (__nv_bfloat16*)dst_bf16, tab);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error("dpack launch", e);
+  return 0;
+}

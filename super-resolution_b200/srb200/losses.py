@@ -41,6 +41,33 @@ def pixel_losses(gen, gt, lr, k, w_hr, w_lr, grad_out, accumulate, work: PixelLo
     return acc[0] / (H * W), acc[1] / (B * (H // k) * (W // k))
 
 
+def ragan_raw(u, v):
+    """One kernel: the relativistic-average loss of RaGAN below plus d loss/d u and d loss/d v (no autograd)."""
+    uc, vc = _c(u), _c(v)
+    B = uc.shape[0]
+    n = uc.numel() // B
+    loss = torch.empty((), device=u.device)
+    gu, gv = torch.empty_like(uc), torch.empty_like(vc)
+    L.check(L.lib().srb_ragan(uc.data_ptr(), vc.data_ptr(), B, n, EPS, loss.data_ptr(), gu.data_ptr(),
+                              gv.data_ptr(), _st()), "ragan")
+    return loss, gu, gv
+
+
+def gradient_penalty_raw(g, coef):
+    """((||g_b||_2 - 1)^2).mean() * coef and its gradient w.r.t. g (esrgan.py:604-605), two small kernels."""
+    gc = _c(g)
+    B = gc.shape[0]
+    n = gc.numel() // B
+    norms = torch.empty(B, device=g.device)
+    loss = torch.zeros((), device=g.device)
+    L.check(L.lib().srb_gp_fwd(gc.data_ptr(), B, n, float(coef), norms.data_ptr(), loss.data_ptr(), _st()), "gp_fwd")
+    gg = torch.empty_like(gc)
+    one = torch.ones((), device=g.device)
+    L.check(L.lib().srb_gp_bwd(gc.data_ptr(), norms.data_ptr(), B, n, float(coef), one.data_ptr(), gg.data_ptr(),
+                               _st()), "gp_bwd")
+    return loss, gg
+
+
 class RaGAN(torch.autograd.Function):
     """0.5*[BCE(eps + u - mean_b v, 1) + BCE(eps + v - mean_b u, 0)]  (esrgan.py:507-508 with u=fake, v=real;
     esrgan.py:578-588 with u=real, v=fake).  Loss and both gradients come out of one kernel."""

@@ -15,6 +15,7 @@ from typing import Dict, List, Optional, Sequence
 
 import torch
 
+from . import disc_engine as DE
 from . import discriminator as D
 from . import losses as LS
 from .optim import FusedAdam
@@ -23,7 +24,7 @@ from .optim import FusedAdam
 class GANTrainStep:
     def __init__(self, generator, discriminators: Sequence, *, factor: int, lambdas=(0.2, 1.0), lambda_hr=1.0,
                  lambda_lr=0.1, lambda_adv=0.01, lambda_reg=0.01, d_threshold=0.001, lr=2e-4, lr_g=0.0, lr_d=0.0,
-                 betas=(0.9, 0.999), l2decay=0.0, scaling_power=1.0, process_group=None):
+                 betas=(0.9, 0.999), l2decay=0.0, scaling_power=1.0, process_group=None, use_disc_engine=True):
         if scaling_power != 1:
             raise RuntimeError("CUDA srb200: the fused train step covers scaling_power == 1 (options/default.json); "
                                "other powers train through the module API + autograd")
@@ -38,6 +39,12 @@ class GANTrainStep:
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self._work = {}
         self._comm_stream = None
+        # tensor-core discriminator engine where the configuration allows it; the general fp32 autograd path otherwise
+        self.d_eng = []
+        for d in self.Ds:
+            ok = (use_disc_engine and d is not None and type(d).__name__ == "Markovian_Discriminator"
+                  and DE.supported(d.model, d.input_shape))
+            self.d_eng.append(DE.DiscEngine(d.model, d.input_shape) if ok else None)
 
     # ------------------------------------------------------------------ helpers
     def _pix_work(self, B, H, W, dev):
@@ -84,13 +91,20 @@ class GANTrainStep:
             if self.lambdas[k] <= 0 or self.Ds[k] is None or self.l_adv <= 0:
                 continue
             d = self.Ds[k]
-            with torch.no_grad():
-                pred_real = D.sequential_forward(d.model, imgs_hr)                        # esrgan.py:493 (.detach())
-            x = generated[k].detach().requires_grad_(True)
-            with torch.enable_grad():
-                pred_fake = D.sequential_forward(d.model, x, detach_params=True)          # esrgan.py:494
-                l_adv = LS.RaGAN.apply(pred_fake, pred_real)                              # esrgan.py:507-508
-                (g_adv,) = torch.autograd.grad(l_adv * (self.lambdas[k] * self.l_adv), x)
+            w_adv = self.lambdas[k] * self.l_adv
+            if self.d_eng[k] is not None:
+                eng_d = self.d_eng[k]
+                A = eng_d.forward([imgs_hr, generated[k]], tag="rf")                       # esrgan.py:493-494 (one 2B batch)
+                l_adv, gu, _ = LS.ragan_raw(A.pred[B:], A.pred[:B])                        # esrgan.py:507-508
+                g_adv, _ = eng_d.input_grad(A, gu * w_adv, B, B, tag="ig")
+            else:
+                with torch.no_grad():
+                    pred_real = D.sequential_forward(d.model, imgs_hr)                    # esrgan.py:493 (.detach())
+                x = generated[k].detach().requires_grad_(True)
+                with torch.enable_grad():
+                    pred_fake = D.sequential_forward(d.model, x, detach_params=True)      # esrgan.py:494
+                    l_adv = LS.RaGAN.apply(pred_fake, pred_real)                          # esrgan.py:507-508
+                    (g_adv,) = torch.autograd.grad(l_adv * w_adv, x)
             g[k].add_(g_adv)
             out_losses[f"adv{k}"] = l_adv.detach()
             loss_G = loss_G + self.lambdas[k] * self.l_adv * l_adv.detach()
@@ -111,17 +125,38 @@ class GANTrainStep:
             opt = self.opt_D[k]
             opt.zero_grad()
             real, fake = imgs_hr, generated[k].detach()
-            pred_real = D.sequential_forward(d.model, real)                                # esrgan.py:569
-            pred_fake = D.sequential_forward(d.model, fake)                                # esrgan.py:570
-            loss_D = LS.RaGAN.apply(pred_real, pred_fake)                                  # esrgan.py:578-588
-            if self.l_reg > 0:
-                eps = epsilons[k].to(dev) if epsilons is not None else torch.rand(B, 1, 1, 1, device=dev)   # 598
-                interp = eps * real + (1 - eps) * fake                                     # 599-600
-                _, gi = D.input_gradient(d.model, interp)                                  # 601-602
-                gp = LS.GradientPenalty.apply(gi.reshape(B, -1), self.l_reg / 2)           # 604-605
-                loss_D = loss_D + gp                                                       # 606
-                out_losses[f"gp{k}"] = gp.detach()
-            loss_D.backward()                                                              # esrgan.py:616
+            if self.d_eng[k] is not None:
+                eng_d = self.d_eng[k]
+                # D_k's weights have not moved since the generator step: its forward over (real, fake) is reused
+                A = eng_d.acts(2 * B, dev, "rf") if (self.lambdas[k] > 0 and self.l_adv > 0) else \
+                    eng_d.forward([real, fake], tag="rf")
+                loss_D, gu, gv = LS.ragan_raw(A.pred[:B], A.pred[B:])                      # esrgan.py:578-588
+                opt.flat_g.zero_()
+                grads = [(opt.grad_views[2 * l], opt.grad_views[2 * l + 1]) for l in range(eng_d.L)]
+                eng_d.backward(A, torch.cat([gu, gv]), grads, tag="bw")
+                if self.l_reg > 0:
+                    eps = epsilons[k].to(dev) if epsilons is not None else torch.rand(B, 1, 1, 1, device=dev)   # 598
+                    interp = eps * real + (1 - eps) * fake                                 # 599-600
+                    Ai = eng_d.forward([interp], tag="gp")                                 # 601
+                    gi, hz = eng_d.input_grad(Ai, torch.ones_like(Ai.pred), 0, B, tag="gph")   # 602
+                    gp, q0 = LS.gradient_penalty_raw(gi.reshape(B, -1), self.l_reg / 2)    # 604-605
+                    eng_d.penalty_backward(Ai, hz, q0.view_as(gi), grads)
+                    loss_D = loss_D + gp                                                   # 606
+                    out_losses[f"gp{k}"] = gp
+                for p_, gv_ in zip(opt.params, opt.grad_views):
+                    p_.grad = gv_
+            else:
+                pred_real = D.sequential_forward(d.model, real)                            # esrgan.py:569
+                pred_fake = D.sequential_forward(d.model, fake)                            # esrgan.py:570
+                loss_D = LS.RaGAN.apply(pred_real, pred_fake)                              # esrgan.py:578-588
+                if self.l_reg > 0:
+                    eps = epsilons[k].to(dev) if epsilons is not None else torch.rand(B, 1, 1, 1, device=dev)   # 598
+                    interp = eps * real + (1 - eps) * fake                                 # 599-600
+                    _, gi = D.input_gradient(d.model, interp)                              # 601-602
+                    gp = LS.GradientPenalty.apply(gi.reshape(B, -1), self.l_reg / 2)       # 604-605
+                    loss_D = loss_D + gp                                                   # 606
+                    out_losses[f"gp{k}"] = gp.detach()
+                loss_D.backward()                                                          # esrgan.py:616
             gate = loss_D.detach().clone()
             opt.gather_grads()
             if self.world > 1:

@@ -1,0 +1,223 @@
+"""GPU parity of the tensor-core discriminator kernels (csrc/disc_mma.cu) and the hand-scheduled engine
+(srb200/disc_engine.py).
+
+Kernel level: operands are rounded to bf16 first, so the comparison against torch's fp32 conv isolates indexing /
+layout errors: tolerance 2e-3 of the output range (bf16 output rounding) for activations, 2e-3 relative for the fp32
+weight gradients.
+Engine level: bf16 kernels against the general fp32 autograd path of srb200/discriminator.py (itself pinned to the
+reference's golden vectors in test_discriminator_gpu.py): predictions within 2e-2 of range, gradients cosine >= 0.995
+(first order) / >= 0.99 (gradient-penalty second order)."""
+import ctypes as C
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch.device("cuda:0")
+
+
+def _cos(a, b):
+    a, b = a.float().cpu().reshape(-1), b.float().cpu().reshape(-1)
+    return torch.dot(a, b).item() / (a.norm().item() * b.norm().item() + 1e-30)
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _pack(w, kind):
+    """Python restatement of srb_dpack for one layer (fp32 OIHW -> bf16 [9][rows][kpad])."""
+    from srb200 import _lib as L
+    co, ci = w.shape[0], w.shape[1]
+    p8 = lambda v: (v + 7) // 8 * 8
+    p16 = lambda v: (v + 15) // 16 * 16
+    rows, kp = (p8(co), p16(ci)) if kind == 0 else (p8(ci), p16(co))
+    out = torch.empty(9 * rows * kp, dtype=torch.bfloat16, device=w.device)
+    src = (C.c_longlong * 1)(0); dst = (C.c_longlong * 1)(0)
+    co_ = (C.c_int * 1)(co); ci_ = (C.c_int * 1)(ci); kd = (C.c_int * 1)(kind)
+    wf = w.detach().float().contiguous()
+    L.check(L.lib().srb_dpack(wf.data_ptr(), out.data_ptr(), 1, C.cast(src, C.c_void_p), C.cast(dst, C.c_void_p),
+                              C.cast(co_, C.c_void_p), C.cast(ci_, C.c_void_p), C.cast(kd, C.c_void_p), _st()))
+    return out
+
+
+def _nhwc(x):      # NCHW fp32 -> NHWC bf16
+    return x.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16)
+
+
+def _nchw(x):      # NHWC bf16 -> NCHW fp32
+    return x.float().permute(0, 3, 1, 2).contiguous()
+
+
+CASES = [  # B, H, W, cin, cout, stride
+    (3, 12, 12, 16, 16, 1), (2, 80, 80, 16, 16, 2), (5, 40, 40, 16, 32, 1), (3, 40, 40, 32, 32, 2),
+    (7, 20, 20, 32, 32, 1), (9, 10, 10, 32, 64, 1), (11, 10, 10, 64, 64, 2), (13, 5, 5, 64, 1, 1),
+    (2, 6, 10, 64, 32, 1), (1, 14, 6, 32, 16, 2), (4, 7, 9, 16, 64, 1),
+]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_dmma_conv_forward_dgrad_wgrad(case):
+    dev = _dev()
+    from srb200 import _lib as L
+    lib = L.lib()
+    B, H, W, ci, co, s = case
+    g = torch.Generator().manual_seed(sum(case))
+    x = torch.randn(B, ci, H, W, generator=g).to(dev).to(torch.bfloat16).float()
+    w = (torch.randn(co, ci, 3, 3, generator=g) / (3 * ci ** 0.5)).to(dev).to(torch.bfloat16).float()
+    b = (torch.randn(co, generator=g) * 0.1).to(dev)
+    Ho, Wo = (H - 1) // s + 1, (W - 1) // s + 1
+    # ---- forward + LeakyReLU
+    ref = F.leaky_relu(F.conv2d(x, w, b, s, 1), 0.2)
+    xh = _nhwc(x)
+    wf = _pack(w, 0)
+    out = torch.zeros(B, Ho, Wo, co, dtype=torch.bfloat16, device=dev)
+    outf = torch.zeros(B, Ho, Wo, device=dev) if co == 1 else None
+    L.check(lib.srb_dmma_conv(xh.data_ptr(), None, ci, wf.data_ptr(), b.data_ptr(), co, out.data_ptr(),
+                              outf.data_ptr() if outf is not None else None, None, B, H, W, Ho, Wo, s, 0, 1, 0.2, _st()))
+    torch.cuda.synchronize()
+    scale = ref.abs().max().item()
+    assert (_nchw(out) - ref).abs().max().item() <= 6e-3 * scale
+    if outf is not None:
+        assert (outf[:, None] - ref).abs().max().item() <= 1e-4 * scale
+    # ---- input gradient with the LeakyReLU' mask of the layer below
+    gz = torch.randn(B, co, Ho, Wo, generator=g).to(dev).to(torch.bfloat16).float()
+    below = torch.randn(B, ci, H, W, generator=g).to(dev).to(torch.bfloat16).float()
+    gx_ref = F.conv_transpose2d(gz, w, None, s, 1, output_padding=(H - ((Ho - 1) * s + 1), W - ((Wo - 1) * s + 1)))
+    gx_ref = gx_ref * torch.where(below > 0, 1.0, 0.2)
+    if s == 1 or (H % 2 == 0 and W % 2 == 0):
+        wd = _pack(w, 1 if s == 1 else 2)
+        gx = torch.zeros(B, H, W, ci, dtype=torch.bfloat16, device=dev)
+        gzh = _nhwc(gz)
+        if co == 1:
+            gzf = gz[:, 0].contiguous()
+            L.check(lib.srb_dmma_conv(None, gzf.data_ptr(), co, wd.data_ptr(), None, ci, gx.data_ptr(), None,
+                                      _nhwc(below).data_ptr(), B, Ho, Wo, H, W, 1, 1 if s == 2 else 0, 2, 0.2, _st()))
+        else:
+            L.check(lib.srb_dmma_conv(gzh.data_ptr(), None, co, wd.data_ptr(), None, ci, gx.data_ptr(), None,
+                                      _nhwc(below).data_ptr(), B, Ho, Wo, H, W, 1, 1 if s == 2 else 0, 2, 0.2, _st()))
+        torch.cuda.synchronize()
+        sc = gx_ref.abs().max().item()
+        assert (_nchw(gx) - gx_ref).abs().max().item() <= 6e-3 * sc
+    # ---- weight / bias gradient (accumulating)
+    wr = w.clone().requires_grad_(True)
+    br = b.clone().requires_grad_(True)
+    F.conv2d(x, wr, br, s, 1).backward(gz)
+    dw = torch.full((co, ci, 3, 3), 0.5, device=dev)
+    db = torch.full((co,), 0.25, device=dev)
+    if co == 1:
+        gzf = gz[:, 0].contiguous()
+        L.check(lib.srb_dmma_wgrad(None, gzf.data_ptr(), co, xh.data_ptr(), ci, dw.data_ptr(), db.data_ptr(), B, H, W,
+                                   Ho, Wo, s, _st()))
+    else:
+        L.check(lib.srb_dmma_wgrad(_nhwc(gz).data_ptr(), None, co, xh.data_ptr(), ci, dw.data_ptr(), db.data_ptr(), B, H,
+                                   W, Ho, Wo, s, _st()))
+    torch.cuda.synchronize()
+    sw = wr.grad.abs().max().item()
+    assert (dw - 0.5 - wr.grad).abs().max().item() <= 2e-3 * sw
+    assert (db - 0.25 - br.grad).abs().max().item() <= 2e-3 * br.grad.abs().max().item() + 1e-4
+
+
+@pytest.mark.parametrize("C1", [16, 32])
+def test_image_end_kernels(C1):
+    dev = _dev()
+    from srb200 import _lib as L
+    lib = L.lib()
+    B, H, W = 5, 18, 22
+    g = torch.Generator().manual_seed(C1)
+    img = torch.randn(B, 1, H, W, generator=g).to(dev)
+    w = (torch.randn(C1, 1, 3, 3, generator=g) / 3).to(dev)
+    b = (torch.randn(C1, generator=g) * 0.1).to(dev)
+    ref = F.leaky_relu(F.conv2d(img, w, b, 1, 1), 0.2)
+    out = torch.zeros(B, H, W, C1, dtype=torch.bfloat16, device=dev)
+    L.check(lib.srb_dl1_fwd(img.data_ptr(), w.data_ptr(), b.data_ptr(), out.data_ptr(), None, C1, B, H, W, 1, 0.2, _st()))
+    torch.cuda.synchronize()
+    assert (_nchw(out) - ref).abs().max().item() <= 5e-3 * ref.abs().max().item()
+    # masked form without bias
+    below = _nhwc(torch.randn(B, C1, H, W, generator=g).to(dev))
+    ref2 = F.conv2d(img, w, None, 1, 1) * torch.where(_nchw(below) > 0, 1.0, 0.2)
+    L.check(lib.srb_dl1_fwd(img.data_ptr(), w.data_ptr(), None, out.data_ptr(), below.data_ptr(), C1, B, H, W, 2, 0.2, _st()))
+    torch.cuda.synchronize()
+    assert (_nchw(out) - ref2).abs().max().item() <= 5e-3 * ref2.abs().max().item()
+    # input gradient
+    gz = torch.randn(B, C1, H, W, generator=g).to(dev).to(torch.bfloat16).float()
+    gx_ref = F.conv_transpose2d(gz, w, None, 1, 1)
+    gx = torch.zeros(B, 1, H, W, device=dev)
+    L.check(lib.srb_dl1_dgrad(_nhwc(gz).data_ptr(), w.data_ptr(), gx.data_ptr(), C1, B, H, W, _st()))
+    torch.cuda.synchronize()
+    assert (gx - gx_ref).abs().max().item() <= 1e-4 * gx_ref.abs().max().item()
+    # weight gradient
+    wr, br = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    F.conv2d(img, wr, br, 1, 1).backward(gz)
+    dw = torch.zeros(C1, 1, 3, 3, device=dev); db = torch.zeros(C1, device=dev)
+    L.check(lib.srb_dl1_wgrad(_nhwc(gz).data_ptr(), img.data_ptr(), dw.data_ptr(), db.data_ptr(), C1, B, H, W, _st()))
+    torch.cuda.synchronize()
+    assert (dw - wr.grad).abs().max().item() <= 1e-4 * wr.grad.abs().max().item()
+    assert (db - br.grad).abs().max().item() <= 1e-4 * br.grad.abs().max().item()
+
+
+def _make_d(dev, seed):
+    import models
+    d = models.Markovian_Discriminator((1, 80, 80), [16, 32, 32, 64])
+    d.load_state_dict(O.make_discriminator_sd(seed, gain=2.0))
+    return d.to(dev)
+
+
+def test_engine_matches_fp32_autograd_path():
+    dev = _dev()
+    from srb200 import disc_engine as DE, losses as LS
+    B = 6
+    d = _make_d(dev, 71)
+    eng = DE.DiscEngine(d.model, d.input_shape)
+    hr, _ = O.synthetic_jets(B, 80, 4, 72)
+    fake, _ = O.synthetic_jets(B, 80, 4, 73)
+    fake = fake * 0.7 + 0.01
+    hr, fake = hr.to(dev), fake.to(dev)
+    # forward
+    A = eng.forward([hr, fake], tag="rf")
+    both = torch.cat([hr, fake]).requires_grad_(True)
+    pred_ref = d(both)
+    scale = pred_ref.abs().max().item()
+    assert (A.pred - pred_ref).abs().max().item() <= 2e-2 * scale
+    # first-order: parameter gradients and the image gradient of <g, D(x)>
+    gp_ = torch.randn(2 * B, 1, 5, 5, generator=torch.Generator().manual_seed(5)).to(dev)
+    params = list(d.parameters())
+    ref_grads = torch.autograd.grad(pred_ref, params + [both], gp_)
+    grads = [(torch.zeros_like(params[2 * l]), torch.zeros_like(params[2 * l + 1])) for l in range(eng.L)]
+    eng.backward(A, gp_, grads, tag="bw")
+    gx, _ = eng.input_grad(A, gp_[B:], B, B, tag="ig")
+    torch.cuda.synchronize()
+    for l in range(eng.L):
+        assert _cos(grads[l][0], ref_grads[2 * l]) >= 0.995, ("w", l, _cos(grads[l][0], ref_grads[2 * l]))
+        assert _cos(grads[l][1], ref_grads[2 * l + 1]) >= 0.995, ("b", l)
+        rn = ref_grads[2 * l].norm().item()
+        assert abs(grads[l][0].norm().item() - rn) <= 3e-2 * rn
+    assert _cos(gx, ref_grads[-1][B:]) >= 0.995
+    # gradient penalty: value and second-order parameter gradients (esrgan.py:596-606)
+    eps = torch.rand(B, 1, 1, 1, generator=torch.Generator().manual_seed(6)).to(dev)
+    interp = (eps * hr + (1 - eps) * fake)
+    xi = interp.clone().requires_grad_(True)
+    pi = d(xi)
+    gi_ref = torch.autograd.grad(pi, xi, torch.ones_like(pi), create_graph=True)[0]
+    gp_ref = ((gi_ref.view(B, -1).norm(2, dim=1) - 1) ** 2).mean() * 0.005
+    ref2 = torch.autograd.grad(gp_ref, [p for p in params if p.dim() == 4])
+    Ai = eng.forward([interp], tag="gp")
+    gi, hz = eng.input_grad(Ai, torch.ones_like(Ai.pred), 0, B, tag="gph")
+    assert _cos(gi, gi_ref) >= 0.995
+    gpv, q0 = LS.gradient_penalty_raw(gi.reshape(B, -1), 0.005)
+    assert abs(gpv.item() - gp_ref.item()) <= 3e-2 * abs(gp_ref.item()) + 1e-7
+    grads2 = [(torch.zeros_like(params[2 * l]), torch.zeros_like(params[2 * l + 1])) for l in range(eng.L)]
+    eng.penalty_backward(Ai, hz, q0.view_as(gi), grads2)
+    torch.cuda.synchronize()
+    for l in range(eng.L):
+        c = _cos(grads2[l][0], ref2[l])
+        assert c >= 0.99, ("gp w", l, c)
+        assert grads2[l][1].abs().max().item() == 0.0
