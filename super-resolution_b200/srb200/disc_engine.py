@@ -249,7 +249,11 @@ class DiscEngine:
             gz_f32 = g_pred if last else None
             if want_wgrad:
                 dw, db = grads[l]
-                self._wgrad(l, gz_bf16, gz_f32, a_in, B, dw, db)
+                if last:        # single fp32 channel: its bias gradient is a plain sum, kept in fp32 so that the
+                    self._wgrad(l, gz_bf16, gz_f32, a_in, B, dw, None)      # relativistic loss's exact cancellation
+                    db.add_(g_pred.sum().reshape(db.shape))                 # (sum of d loss / d pred == 0) survives
+                else:
+                    self._wgrad(l, gz_bf16, gz_f32, a_in, B, dw, db)
             self._dgrad(l, gz_bf16, gz_f32, ch[l - 1], B, ref=a_in, slope=self.slopes[l - 1])
         return ch
 
