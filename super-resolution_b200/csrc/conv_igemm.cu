@@ -22,10 +22,12 @@
 
 namespace srb {
 
-constexpr int kIgemmThreads = 192;
-constexpr int kBSlots = 12;          // weight-tile ring (8 KB each)
+constexpr int kIgemmThreads = 288;   // warp 0 TMA producer, warps 1-4 MMA issuers, warps 5-8 epilogue
+constexpr int kIssuers = 4;
+constexpr int kBSlots = 4;           // weight ring: one slot = the three taps of one filter row (3 x 8 KB)
 constexpr int kAStages = 2;          // halo-window ring
 constexpr int kBTileBytes = 64 * 64 * 2;
+constexpr int kBSlotBytes = 3 * kBTileBytes;
 
 struct IgemmParams {
   int R;            // total flat rows = batch * P
@@ -48,6 +50,7 @@ struct IgemmParams {
   const __nv_bfloat16* res1; int res1_cstride, res1_coff; float res1_scale;
   const __nv_bfloat16* res2; int res2_cstride, res2_coff; float res2_scale;
   int base_offset_mode;
+  int dbg;          // timing experiments only (flags >> 1): 1 no weight reloads, 2 no activation reloads, 4 no epilogue I/O
 };
 
 __device__ __forceinline__ void load_row64(const __nv_bfloat16* p, uint4 (&v)[8]) {
@@ -65,7 +68,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a_smem = smem;
   uint8_t* b_smem = a_smem + kAStages * p.a_stage_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(b_smem + kBSlots * kBTileBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(b_smem + kBSlots * kBSlotBytes);
   uint64_t* a_full = bars;                      // [kAStages]
   uint64_t* a_empty = a_full + kAStages;        // [kAStages]
   uint64_t* b_full = a_empty + kAStages;        // [kBSlots]
@@ -76,14 +79,16 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  constexpr uint32_t kTmemCols = 2 * 64 * MT;   // 128 or 256: power of two
+  // four accumulators (one per issuer warp) of 64 columns, double buffered: all 512 TMEM columns
+  constexpr uint32_t kTmemCols = 512;
+  constexpr int NACC = kIssuers / MT;           // accumulators that sum to one 128-row sub-tile
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_x);
     tma_prefetch_desc(&tmap_w);
-    for (int i = 0; i < kAStages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], 1); }
-    for (int i = 0; i < kBSlots; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&t_full[i], 1); mbar_init(&t_empty[i], 4); }
+    for (int i = 0; i < kAStages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], kIssuers); }
+    for (int i = 0; i < kBSlots; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], kIssuers); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&t_full[i], kIssuers); mbar_init(&t_empty[i], 4); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
@@ -104,59 +109,81 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         const int q0 = mt_idx * rows_per_tile;
         for (int kb = 0; kb < p.KB; ++kb) {
           mbar_wait(&a_empty[sa], pa ^ 1, 1);
+          if ((p.dbg & 2) && (work != blockIdx.x || kb >= kAStages)) mbar_arrive(&a_full[sa]);
+          else {
           mbar_expect_tx(&a_full[sa], p.a_stage_bytes);
           for (int bx = 0; bx < p.a_nbox; ++bx)
             tma_load_2d(a_smem + sa * p.a_stage_bytes + bx * p.a_box_rows * 128, &tmap_x, p.x_coff + kb * 64,
                         q0 - p.halo + bx * p.a_box_rows, &a_full[sa]);
+          }
           if (++sa == kAStages) { sa = 0; pa ^= 1; }
-          for (int t = 0; t < 9; ++t) {
+          for (int dy = 0; dy < 3; ++dy) {
             mbar_wait(&b_empty[sb], pb ^ 1, 2);
-            mbar_expect_tx(&b_full[sb], kBTileBytes);
-            tma_load_2d(b_smem + sb * kBTileBytes, &tmap_w, 0, (t * p.KB + kb) * p.cout + nt * 64, &b_full[sb]);
+            if ((p.dbg & 1) && (work != blockIdx.x || kb > 0)) { mbar_arrive(&b_full[sb]); }
+            else {
+              mbar_expect_tx(&b_full[sb], kBSlotBytes);
+              for (int dx = 0; dx < 3; ++dx)
+                tma_load_2d(b_smem + sb * kBSlotBytes + dx * kBTileBytes, &tmap_w, 0,
+                            ((dy * 3 + dx) * p.KB + kb) * p.cout + nt * 64, &b_full[sb]);
+            }
             if (++sb == kBSlots) { sb = 0; pb ^= 1; }
           }
         }
       }
     }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    constexpr uint32_t idesc = make_idesc_bf16(128, 64, 0, 0);
-    uint32_t sa = 0, pa = 0, sb = 0, pb = 0, as = 0, pt = 0;
-    for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
-      mbar_wait(&t_empty[as], pt ^ 1, 3);
-      tc_fence_after();
-      for (int kb = 0; kb < p.KB; ++kb) {
-        mbar_wait(&a_full[sa], pa, 4);
-        const uint32_t a_base = smem_u32(a_smem + sa * p.a_stage_bytes);
-        for (int t = 0; t < 9; ++t) {
-          mbar_wait(&b_full[sb], pb, 5);
-          tc_fence_after();
-          if (elect_one()) {
-            const int shift = p.halo + (t / 3 - 1) * p.pitch + (t % 3 - 1);
-            const uint32_t b_base = smem_u32(b_smem + sb * kBTileBytes);
+  } else if (warp <= kIssuers) {
+    // ------------------------------------------------------------------ MMA issuers (warps 1..4, one thread each)
+    // A single thread sustains roughly one tcgen05.mma per 100 clk through the descriptor arithmetic and the
+    // barrier traffic, but a 128x64x16 MMA only occupies the tensor pipe for 32 clk (tools/probe1.py rate).  So the
+    // issue work is split over four warps on four different schedulers.  MMAs from different threads are unordered,
+    // hence every issuer owns a private 64-column accumulator (no "first MMA clears" hazard); the epilogue adds them.
+    //   MT == 2: issuer i -> sub-tile i >> 1, k-steps {2(i&1), 2(i&1)+1};   MT == 1: issuer i -> k-step i.
+    if (lane == 0) {
+      const int iss = warp - 1;
+      const int mt = MT == 2 ? (iss >> 1) : 0;
+      const int k0 = MT == 2 ? 2 * (iss & 1) : iss;
+      constexpr int NK = MT == 2 ? 2 : 1;
+      constexpr uint32_t idesc = make_idesc_bf16(128, 64, 0, 0);
+      constexpr uint64_t desc_hi = (uint64_t(16 >> 4) << 16) | (uint64_t(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+      const uint32_t a0 = ((smem_u32(a_smem) & 0x3FFFFu) >> 4) + mt * 1024 + k0 * 2;
+      const uint32_t b0 = ((smem_u32(b_smem) & 0x3FFFFu) >> 4) + k0 * 2;
+      const uint32_t a_stage16 = p.a_stage_bytes >> 4;
+      uint32_t sa = 0, pa = 0, sb = 0, pb = 0, as = 0, pt = 0;
+      for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
+        mbar_wait(&t_empty[as], pt ^ 1, 3);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * 256 + iss * 64;
+        for (int kb = 0; kb < p.KB; ++kb) {
+          mbar_wait(&a_full[sa], pa, 4);
+          const uint32_t a_lo = a0 + sa * a_stage16;
+          uint32_t row16 = static_cast<uint32_t>(p.halo - p.pitch - 1) * 8u;     // tap (-1,-1), in 16-byte units
+#pragma unroll 1
+          for (int dy = 0; dy < 3; ++dy) {
+            mbar_wait(&b_full[sb], pb, 5);
+            tc_fence_after();
+            const uint32_t b_lo = b0 + sb * (kBSlotBytes >> 4);
 #pragma unroll
-            for (int mt = 0; mt < MT; ++mt) {
-              const uint32_t a_tap = a_base + static_cast<uint32_t>(shift + mt * 128) * 128u;
+            for (int dx = 0; dx < 3; ++dx) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                const uint64_t ad = make_sw128_desc(a_tap + k * 32, 16, 1024, p.base_offset_mode);
-                const uint64_t bd = make_sw128_desc(b_base + k * 32, 16, 1024, 0);
-                umma_bf16(tmem_base + as * (64 * MT) + mt * 64, ad, bd, idesc, (kb | t | k) != 0);
+              for (int k = 0; k < NK; ++k) {
+                const uint64_t ad = desc_hi | static_cast<uint64_t>(a_lo + row16 + dx * 8 + k * 2);
+                const uint64_t bd = desc_hi | static_cast<uint64_t>(b_lo + dx * (kBTileBytes >> 4) + k * 2);
+                umma_bf16(d_tmem, ad, bd, idesc, (dx | k) != 0 ? 1u : static_cast<uint32_t>((kb | dy) != 0));
               }
             }
             umma_commit(&b_empty[sb]);
-            if (t == 8) umma_commit(&a_empty[sa]);
-            if (t == 8 && kb == p.KB - 1) umma_commit(&t_full[as]);
+            row16 += static_cast<uint32_t>(p.pitch) * 8u;
+            if (++sb == kBSlots) { sb = 0; pb ^= 1; }
           }
-          __syncwarp();
-          if (++sb == kBSlots) { sb = 0; pb ^= 1; }
+          umma_commit(&a_empty[sa]);
+          if (kb == p.KB - 1) umma_commit(&t_full[as]);
+          if (++sa == kAStages) { sa = 0; pa ^= 1; }
         }
-        if (++sa == kAStages) { sa = 0; pa ^= 1; }
+        if (++as == 2) { as = 0; pt ^= 1; }
       }
-      if (++as == 2) { as = 0; pt ^= 1; }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue warps 2..5
+    // ------------------------------------------------------------------ epilogue warps 5..8
     const int lg = warp & 3;                    // TMEM lane group this warp may access
     uint32_t as = 0, pt = 0;
     for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
@@ -169,8 +196,8 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         const int q = mt_idx * rows_per_tile + mt * 128 + lg * 32 + lane;
         const int r = q % p.P;
         const int py = r / p.pitch, px = r - py * p.pitch;
-        const bool valid = (q < p.R) && (px < p.W) && (py < p.H);
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + as * (64 * MT) + mt * 64;
+        const bool valid = (q < p.R) && (px < p.W) && (py < p.H) && !(p.dbg & 4);
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + as * 256 + mt * (NACC * 64);
         const int n0 = nt * 64;
         // destination row
         size_t yrow;
@@ -188,14 +215,23 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         }
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
-          uint32_t acc[32];
-          tmem_ld32(taddr + half * 32, acc);
-          tmem_ld_wait();
-          if (valid) {
-            const int c0 = n0 + half * 32;
-            float v[32];
+          float v[32];
+          {
+            uint32_t acc[32];
+            tmem_ld32(taddr + half * 32, acc);
+            tmem_ld_wait();
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]);
+#pragma unroll
+            for (int j = 1; j < NACC; ++j) {
+              tmem_ld32(taddr + j * 64 + half * 32, acc);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] += __uint_as_float(acc[i]);
+            }
+          }
+          if (valid) {
+            const int c0 = n0 + half * 32;
             if (p.bias) {
               const float4* b4 = reinterpret_cast<const float4*>(p.bias + c0);
 #pragma unroll
@@ -281,7 +317,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 
 // ---------------------------------------------------------------------------------- host side
 static size_t igemm_smem_bytes(uint32_t a_stage_bytes) {
-  return 1024 + size_t(kAStages) * a_stage_bytes + size_t(kBSlots) * kBTileBytes + 512;
+  return 1024 + size_t(kAStages) * a_stage_bytes + size_t(kBSlots) * kBSlotBytes + 512;
 }
 
 int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
@@ -333,6 +369,7 @@ int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   p.res1 = (const __nv_bfloat16*)a->res1; p.res1_cstride = a->res1_cstride; p.res1_coff = a->res1_coff; p.res1_scale = a->res1_scale;
   p.res2 = (const __nv_bfloat16*)a->res2; p.res2_cstride = a->res2_cstride; p.res2_coff = a->res2_coff; p.res2_scale = a->res2_scale;
   p.base_offset_mode = a->flags & 1;
+  p.dbg = a->flags >> 1;
   if (p.act == SRB_ACT_LRELU_MASK && !p.mask) return set_error("conv3x3: mask activation without mask tensor");
 
   const int grid = p.num_work < sms ? p.num_work : sms;

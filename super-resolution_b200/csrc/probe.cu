@@ -51,6 +51,18 @@ __global__ void __launch_bounds__(128, 1) probe_mma_kernel(const ProbeParams p) 
         const int k = i & 3;
         const int acc = (i >> 2) & 1;
         uint64_t ad, bd;
+        if (p.a_row_shift < 0) {
+          // replica of the conv kernel's issue order: 9 taps x 2 sub-tiles x 4 k-steps, 12 weight slots, pitch 21
+          const int mt = (i >> 2) & 1, t = (i >> 3) % 9, slot = (i >> 3) % 12;
+          const int variant = -p.a_row_shift;           // 1: all as in the kernel, 2: fixed A window, 3: fixed B slot
+          const int shift = variant == 2 ? 0 : 22 + (t / 3 - 1) * 21 + (t % 3 - 1);
+          const uint32_t aa = smem_u32(smem) + (shift + mt * 128) * 128 + k * 32;
+          const uint32_t bb = smem_u32(smem) + 40 * 1024 + (variant == 3 ? 0 : slot) * 4096 + k * 32;
+          ad = make_sw128_desc(aa, 16, 1024, 0);
+          bd = make_sw128_desc(bb, 16, 1024, 0);
+          if (CG == 1) umma_bf16(tmem_base + mt * 64, ad, bd, idesc, 1);
+          continue;
+        }
         if (p.a_mn_major) {
           ad = make_sw128_desc(a_base + k * 2048, 8192, 1024, 0);
           bd = make_sw128_desc(b_base + k * 2048, p.b_lbo, 1024, 0);

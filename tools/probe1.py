@@ -166,7 +166,7 @@ def sec_rate(_):
     lib = L.lib()
     cyc = torch.zeros(148, dtype=torch.int64, device="cuda")
     iters = 4096
-    for (cg, N, shift, mn, lbo) in [(1, 64, 0, 0, 0), (1, 64, 3, 0, 0), (1, 128, 0, 0, 0), (1, 256, 0, 0, 0),
+    for (cg, N, shift, mn, lbo) in [(1, 64, -1, 0, 0), (1, 64, -2, 0, 0), (1, 64, -3, 0, 0), (1, 64, 0, 0, 0), (1, 64, 3, 0, 0), (1, 128, 0, 0, 0), (1, 256, 0, 0, 0),
                                     (2, 64, 0, 0, 0), (2, 128, 0, 0, 0), (2, 256, 0, 0, 0),
                                     (1, 192, 0, 1, 128), (1, 192, 0, 1, 8192), (1, 64, 0, 1, 8192)]:
         for n_ctas in (2, 148):
