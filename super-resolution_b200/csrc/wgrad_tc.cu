@@ -18,7 +18,8 @@
 
 namespace srb {
 
-constexpr int kWgThreads = 192;
+constexpr int kWgThreads = 224;                 // warp 0 TMA, warps 1-2 MMA issuers, warps 3-6 epilogue / bias sums
+constexpr int kWgIssuers = 2;
 constexpr int kWgKc = 64;                       // pixels per pipeline stage
 constexpr int kWgStages = 6;
 constexpr int kWgXBytes = 2 * kWgKc * 128;      // two 64-channel boxes
@@ -36,6 +37,9 @@ struct WgradParams {
   int x_coff, gy_coff;
   float* ws;         // [splits][9][n_cp*128][cout]
   int base_offset_mode;
+  float* dbias;      // bias gradient (atomically accumulated by the cp == 0, dy == 0 work items) or null
+  float alpha;
+  int unshuffle;
 };
 
 __global__ void __launch_bounds__(kWgThreads, 1)
@@ -62,15 +66,16 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   int c_end = c_begin + p.chunks_per_split;
   if (c_end > n_chunks_total) c_end = n_chunks_total;
   const int n_chunks = c_end > c_begin ? c_end - c_begin : 0;
+  const bool do_bias = p.dbias != nullptr && cp == 0 && dyi == 1;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_x);
     tma_prefetch_desc(&tmap_g);
-    for (int i = 0; i < kWgStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    mbar_init(done, 1);
+    for (int i = 0; i < kWgStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], kWgIssuers + (do_bias ? 4 : 0)); }
+    mbar_init(done, kWgIssuers);
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 256);
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -90,32 +95,65 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
         if (++s == kWgStages) { s = 0; ph ^= 1; }
       }
     }
-  } else if (warp == 1) {
-    constexpr uint32_t idesc = make_idesc_bf16(128, 192, 1, 1);
-    uint32_t s = 0, ph = 0;
-    for (int c = 0; c < n_chunks; ++c) {
-      mbar_wait(&full[s], ph, 12);
-      tc_fence_after();
-      if (elect_one()) {
-        const uint32_t xa = smem_u32(smem + s * kWgStageBytes);
-        const uint32_t ga = xa + kWgXBytes;
+  } else if (warp <= kWgIssuers) {
+    // two issuer threads (see conv_igemm.cu): issuer i takes k-steps {2i, 2i+1} of every 64-pixel chunk and owns a
+    // private 192-column accumulator; the epilogue adds the two.
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, 192, 1, 1);
+      constexpr uint64_t a_hi = (uint64_t((kWgKc * 128) >> 4) << 16) | (uint64_t(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+      constexpr uint64_t b_hi = (uint64_t(128 >> 4) << 16) | (uint64_t(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+      const int iss = warp - 1;
+      const uint32_t d_tmem = tmem_base + iss * 192;
+      const uint32_t x0 = ((smem_u32(smem) & 0x3FFFFu) >> 4) + iss * 2 * (2048 >> 4);
+      uint32_t s = 0, ph = 0;
+      for (int c = 0; c < n_chunks; ++c) {
+        mbar_wait(&full[s], ph, 12);
+        tc_fence_after();
+        const uint32_t xa = x0 + s * (kWgStageBytes >> 4);
+        const uint32_t ga = xa + (kWgXBytes >> 4);
 #pragma unroll
-        for (int k = 0; k < kWgKc / 16; ++k) {
-          const uint64_t ad = make_sw128_desc(xa + k * 2048, kWgKc * 128, 1024, 0);
-          const uint64_t bd = make_sw128_desc(ga + k * 2048, 128, 1024, p.base_offset_mode);
-          umma_bf16(tmem_base, ad, bd, idesc, (c | k) != 0);
+        for (int k = 0; k < 2; ++k) {
+          const uint64_t ad = a_hi | static_cast<uint64_t>(xa + k * (2048 >> 4));
+          const uint64_t bd = b_hi | static_cast<uint64_t>(ga + k * (2048 >> 4));
+          umma_bf16(d_tmem, ad, bd, idesc, k != 0 ? 1u : static_cast<uint32_t>(c != 0));
         }
         umma_commit(&empty[s]);
         if (c == n_chunks - 1) umma_commit(done);
+        if (++s == kWgStages) { s = 0; ph ^= 1; }
       }
-      __syncwarp();
-      if (++s == kWgStages) { s = 0; ph ^= 1; }
     }
   } else {
     const int lg = warp & 3;
     const int row = lg * 32 + lane;               // M index = input channel within the pair
     const int ci = cp * 128 + row;
     const int cin_pad = p.n_cp * 128;
+    if (do_bias) {
+      // bias gradient = column sums of gy.  These warps idle during the main loop, so they read the gradient window
+      // of every stage straight out of (128B-swizzled) shared memory: rows 1..64 of the dy == 0 window are exactly the
+      // chunk's own pixels.  Warp lg sums 16 rows, lane = channel pair.
+      float s0 = 0.f, s1 = 0.f;
+      uint32_t s = 0, ph = 0;
+      const int pair = lane;
+      for (int c = 0; c < n_chunks; ++c) {
+        mbar_wait(&full[s], ph, 14);
+        const uint8_t* gw = smem + s * kWgStageBytes + kWgXBytes;
+#pragma unroll 4
+        for (int j = 0; j < 16; ++j) {
+          const int r = 1 + lg * 16 + j;
+          const uint32_t v = *reinterpret_cast<const uint32_t*>(gw + r * 128 + ((((pair >> 2) ^ (r & 7)) << 4) | ((pair & 3) << 2)));
+          s0 += bf16lo(v); s1 += bf16hi(v);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+        if (++s == kWgStages) { s = 0; ph ^= 1; }
+      }
+      const int cq = p.cout / 4;
+      const int co = cb * 64 + pair * 2;
+      const int d0 = p.unshuffle ? (4 * (co % cq) + co / cq) : co;
+      const int d1 = p.unshuffle ? (4 * ((co + 1) % cq) + (co + 1) / cq) : co + 1;
+      atomicAdd(p.dbias + d0, p.alpha * s0);
+      atomicAdd(p.dbias + d1, p.alpha * s1);
+    }
     if (n_chunks > 0) {
       mbar_wait(done, 0, 13);
       tc_fence_after();
@@ -126,19 +164,22 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
       float* dst = p.ws + ((static_cast<size_t>(split) * 9 + t) * cin_pad + ci) * p.cout + cb * 64;
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
-        uint32_t acc[32];
+        uint32_t acc[32], acc2[32];
         if (n_chunks > 0) {
           tmem_ld32(tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + j * 64 + half * 32, acc);
+          tmem_ld32(tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + 192 + j * 64 + half * 32, acc2);
           tmem_ld_wait();
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) acc[i] = 0u;
+          for (int i = 0; i < 32; ++i) { acc[i] = 0u; acc2[i] = 0u; }
         }
         float4* d4 = reinterpret_cast<float4*>(dst + half * 32);
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-          d4[i] = make_float4(__uint_as_float(acc[4 * i]), __uint_as_float(acc[4 * i + 1]),
-                              __uint_as_float(acc[4 * i + 2]), __uint_as_float(acc[4 * i + 3]));
+          d4[i] = make_float4(__uint_as_float(acc[4 * i]) + __uint_as_float(acc2[4 * i]),
+                              __uint_as_float(acc[4 * i + 1]) + __uint_as_float(acc2[4 * i + 1]),
+                              __uint_as_float(acc[4 * i + 2]) + __uint_as_float(acc2[4 * i + 2]),
+                              __uint_as_float(acc[4 * i + 3]) + __uint_as_float(acc2[4 * i + 3]));
       }
     }
   }
@@ -146,7 +187,7 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 256);
+    tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -197,7 +238,8 @@ static void wgrad_plan(long long R, int cin, int cout, int* splits, int* chunks_
   const int n_cp = (cin + 127) / 128, n_cb = cout / 64;
   const int units = n_cp * n_cb * 3;
   const int chunks = int((R + kWgKc - 1) / kWgKc);
-  int s = (2 * sm_count() + units - 1) / units;       // ~2 CTAs worth of work items per SM
+  int s = sm_count() / units;                         // one CTA per SM (150 KB of smem each), one wave, no tail wave
+  if (s < 1) s = 1;
   const int max_s = (chunks + 7) / 8;                 // at least 8 chunks per split
   if (s > max_s) s = max_s;
   if (s < 1) s = 1;
@@ -226,6 +268,8 @@ int wgrad3x3_tc_launch(const srb_wgrad3x3_args* a, cudaStream_t stream) {
   p.R = (int)R; p.pitch = pitch; p.cin = a->cin; p.cout = a->cout; p.n_cp = n_cp; p.n_cb = n_cb;
   p.splits = splits; p.chunks_per_split = cps; p.x_coff = a->x_coff; p.gy_coff = a->gy_coff;
   p.ws = (float*)a->workspace; p.base_offset_mode = a->flags & 1;
+  p.dbias = a->dbias; p.alpha = a->alpha; p.unshuffle = a->unshuffle;
+  if (a->dbias && !a->accumulate) cudaMemsetAsync(a->dbias, 0, sizeof(float) * a->cout, stream);
 
   static bool attr = false;
   const size_t smem = 1024 + size_t(kWgStages) * kWgStageBytes + 256;
@@ -239,16 +283,6 @@ int wgrad3x3_tc_launch(const srb_wgrad3x3_args* a, cudaStream_t stream) {
                                                                 a->accumulate, a->unshuffle, a->dw);
   e = cudaGetLastError();
   if (e != cudaSuccess) return set_cuda_error("wgrad_reduce launch", e);
-  if (a->dbias) {
-    if (!a->accumulate) cudaMemsetAsync(a->dbias, 0, sizeof(float) * a->cout, stream);
-    int slices = int(R / 256); if (slices < 1) slices = 1;
-    const int max_slices = 4 * sm_count() / (a->cout / 64); if (slices > max_slices) slices = max_slices;
-    dim3 g(a->cout / 64, slices);
-    colsum_kernel<<<g, 256, 0, stream>>>((const __nv_bfloat16*)a->gy, (int)R, a->gy_cstride, a->gy_coff, a->cout,
-                                         a->alpha, a->accumulate, a->unshuffle, a->dbias);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return set_cuda_error("colsum launch", e);
-  }
   return 0;
 }
 
