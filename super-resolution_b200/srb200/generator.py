@@ -53,6 +53,7 @@ class GeneratorEngine:
         self._packs_bwd_ready = False
         self._saved = None
         self.grad_views = None       # optional name -> fp32 view: where backward writes parameter gradients
+        self.ready_hook = None       # optional callable(param_name): gradients of this and all later parameters are final
         self.names3x3 = self._conv_names()
 
     # ------------------------------------------------------------------ parameter bookkeeping
@@ -282,8 +283,10 @@ class GeneratorEngine:
                                      bf.hr.data_ptr(), F_, 0, G_SLOPE, bf.gz_scratch.data_ptr(), bf.g_hr.data_ptr(),
                                      F_, 0, bf.grads["conv3.2.weight"].data_ptr(), bf.grads["conv3.2.bias"].data_ptr(),
                                      _st()), "conv_out_bwd")
+        hook = self.ready_hook or (lambda name: None)
         # conv3.0
         self._wgrad(bf, top_in, F_, bf.g_hr, 0, F_, "conv3.0")
+        hook("conv3.0.weight")
         if self.nup:
             self._dconv(bf.g_hr, F_, self.wd["conv3.0"], bf.g_up[-1], 0, F_, act=L.ACT_LRELU_MASK, slope=G_SLOPE,
                         mask=(bf.up[-1], 0))
@@ -297,6 +300,7 @@ class GeneratorEngine:
             name = f"upsampling.{3 * u}"
             x_in = bf.feat if u == 0 else bf.up[u - 1]
             self._wgrad(bf, x_in, F_, bf.g_uns[u], 0, 4 * F_, name, unshuffle=True)
+            hook(name + ".weight")
             if u == 0:
                 self._dconv(bf.g_uns[u], 4 * F_, self.wd[name], bf.g_s, 0, F_)
             else:
@@ -304,6 +308,7 @@ class GeneratorEngine:
                             slope=G_SLOPE, mask=(bf.up[u - 1], 0))
         # conv2 (+ the long skip: g_s also flows straight into conv1's output, added in conv_in_bwd)
         self._wgrad(bf, bf.trunk, F_, bf.g_s, 0, F_, "conv2")
+        hook("conv2.weight")
         self._dconv(bf.g_s, F_, self.wd["conv2"], bf.G[2], 0, F_)
         # RRDB trunk, last to first
         for i in range(self.nb - 1, -1, -1):
@@ -327,6 +332,7 @@ class GeneratorEngine:
                 for k in range(1, 6):
                     self._wgrad(bf, gb, k * F_, G, (5 - k) * F_ if k < 5 else 0, F_, base + f"b{k}.0",
                                 alpha=s5 if k == 5 else 1.0)
+            hook(f"res_blocks.{i}.dense_blocks.0.b1.0.weight")
         # conv1 (models.py:63,122-123): weight gradient from g_out1 + g_s
         L.check(lib.srb_conv_in_bwd(img.data_ptr(), B, ch, h, w, sv["multiplier"], sv["power"], bf.g_out1.data_ptr(),
                                     F_, 0, bf.g_s.data_ptr(), F_, 0, F_, bf.grads["conv1.weight"].data_ptr(),

@@ -32,6 +32,7 @@ class FusedAdam:
             offs.append(n)
             n += (p.numel() + 3) // 4 * 4
         self.n = n
+        self.offsets = offs                      # start of each trainable parameter in the flat buffers
         self.flat_p = torch.zeros(n, device=dev)
         self.flat_g = torch.zeros(n, device=dev)
         self.flat_m = torch.zeros(n, device=dev)

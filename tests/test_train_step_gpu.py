@@ -137,3 +137,39 @@ def test_gan_step_matches_oracle():
     # parameters actually moved (Adam applied; loss_D is far above d_threshold here)
     assert not torch.equal(G.conv2.weight.detach().cpu(), sd_g["conv2.weight"])
     assert not torch.equal(Ds[0].model[0].weight.detach().cpu(), sd_d[0]["model.0.weight"])
+
+
+def test_graphed_step_matches_eager():
+    """The CUDA-graph replay of the iteration trains exactly like the eagerly launched one (gradient penalty off so
+    that no random draw is involved; tolerance covers the order of the fp32 atomics in the weight-gradient kernels)."""
+    dev = _dev()
+    import models
+    from srb200.train_step import GANTrainStep, GraphedStep
+    hr, lr = O.synthetic_jets(4, 80, 4, 91)
+    hr, lr = hr.to(dev), lr.to(dev)
+
+    def make():
+        G = models.GeneratorRRDB(1, filters=64, num_res_blocks=1, num_upsample=2, res_scale=0.1)
+        G.load_state_dict(O.make_generator_sd(92, num_res_blocks=1, num_upsample=2)); G = G.to(dev).train()
+        Ds = []
+        for k in range(2):
+            d = models.Markovian_Discriminator((1, 80, 80), [16, 32, 32, 64])
+            d.load_state_dict(O.make_discriminator_sd(93 + k, gain=2.0)); Ds.append(d.to(dev))
+        return GANTrainStep(G, Ds, factor=4, lambda_reg=0.0)
+
+    eager = make()
+    for _ in range(4):
+        le = eager.step(lr, hr)
+    gr = GraphedStep(make(), lr, hr, warmup=2)        # two eager steps inside, then the capture (not executed)
+    for _ in range(2):
+        lg = gr.step(lr, hr)
+    torch.cuda.synchronize()
+    for k in ("g_loss", "d_loss0", "d_loss1", "hr0", "adv1"):
+        assert abs(le[k].item() - lg[k].item()) <= 1e-3 * abs(le[k].item()) + 1e-6, (k, le[k].item(), lg[k].item())
+    # Adam moves every weight by ~lr = 2e-4 per step in the direction of sign-like ratios m/sqrt(v): where a gradient
+    # is at rounding-noise level the fp32 atomics' order can flip that direction, so single weights may differ by a few
+    # lr; the bulk must agree.
+    for a, b in ((eager.opt_G.flat_p, gr.tr.opt_G.flat_p), (eager.opt_D[0].flat_p, gr.tr.opt_D[0].flat_p)):
+        d = (a - b).abs()
+        assert d.max().item() <= 4 * 4 * 2e-4, d.max().item()
+        assert d.mean().item() <= 2e-5, d.mean().item()
