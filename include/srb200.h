@@ -91,6 +91,12 @@ int srb_pack_conv3x3_fwd(const float* w_oihw, int cout, int cin, int shuffle, fl
 int srb_pack_conv3x3_dgrad(const float* w_oihw, int cout, int cin, int ci_off, int n_out, int unshuffle,
                            float scale, void* wp, int kb_dst, int kb_total, void* stream);
 
+/* Table-driven form of the two packs above: one launch for a whole model.  `items_dev` = device array of
+ *   struct { const float* w; void* wp; int cout, cin, ci_off, n_out, flag, kind, kb_dst, kb_total; float scale; int pad; }
+ * (kind 0: srb_pack_conv3x3_fwd with flag = shuffle; kind 1: srb_pack_conv3x3_dgrad with flag = unshuffle);
+ * `block_prefix_dev[i]` = first 256-thread block of item i, `total_blocks` = sum of ceil(elements_i / 256). */
+int srb_pack_batch(const void* items_dev, const int* block_prefix_dev, int n_items, int total_blocks, void* stream);
+
 /* ---- weight gradient of the same convolution -------------------------------------------------
  * Replaces aten::convolution_backward (filter part) for every 64-multiple conv of the generator.
  *   dw[co][ci][t] (+)= alpha * sum_pixels gy[p][co] * x[p + shift_t][ci];   dbias[co] (+)= alpha * sum gy

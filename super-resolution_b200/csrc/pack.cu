@@ -39,7 +39,64 @@ __global__ void pack_dgrad_kernel(const float* __restrict__ w, int cout, int cin
   wp[(((size_t)t * kb_total + kb_dst + kb) * n_out + n) * 64 + k] = __float2bfloat16(v);
 }
 
+// Table-driven form: one launch re-packs every convolution of a model (608 items for the default generator).
+// blocks are assigned to items through an exclusive prefix of per-item block counts (binary search).
+struct PackItem {
+  const float* w; __nv_bfloat16* wp;
+  int cout, cin, ci_off, n_out;
+  int flag;      // fwd: shuffle; dgrad: unshuffle
+  int kind;      // 0 forward pack, 1 dgrad pack
+  int kb_dst, kb_total;
+  float scale; int pad;
+};
+
+__global__ void pack_batch_kernel(const PackItem* __restrict__ items, const int* __restrict__ prefix, int n_items) {
+  int lo = 0, hi = n_items - 1;
+  while (lo < hi) {                               // last item whose first block <= blockIdx.x
+    const int mid = (lo + hi + 1) >> 1;
+    if (prefix[mid] <= (int)blockIdx.x) lo = mid; else hi = mid - 1;
+  }
+  const PackItem it = items[lo];
+  const long long idx = (blockIdx.x - prefix[lo]) * (long long)blockDim.x + threadIdx.x;
+  if (it.kind == 0) {
+    const long long total = 9LL * it.cout * it.cin;
+    if (idx >= total) return;
+    const int k = int(idx % 64);
+    long long r = idx / 64;
+    const int n = int(r % it.cout); r /= it.cout;
+    const int KB = it.cin / 64;
+    const int kb = int(r % KB);
+    const int t = int(r / KB);
+    const int C = it.cout / 4;
+    const int co = it.flag ? (4 * (n % C) + n / C) : n;
+    it.wp[idx] = __float2bfloat16(it.scale * it.w[((size_t)co * it.cin + kb * 64 + k) * 9 + t]);
+  } else {
+    const long long total = 9LL * it.cout * it.n_out;
+    if (idx >= total) return;
+    const int k = int(idx % 64);
+    long long r = idx / 64;
+    const int n = int(r % it.n_out); r /= it.n_out;
+    const int KBs = it.cout / 64;
+    const int kb = int(r % KBs);
+    const int t = int(r / KBs);
+    const int kk = kb * 64 + k;
+    const int C = it.cout / 4;
+    const int co = it.flag ? (4 * (kk % C) + kk / C) : kk;
+    const float v = it.scale * it.w[((size_t)co * it.cin + it.ci_off + n) * 9 + (8 - t)];
+    it.wp[(((size_t)t * it.kb_total + it.kb_dst + kb) * it.n_out + n) * 64 + k] = __float2bfloat16(v);
+  }
+}
+
 }  // namespace srb
+
+extern "C" int srb_pack_batch(const void* items_dev, const int* block_prefix_dev, int n_items, int total_blocks,
+                              void* stream) {
+  using namespace srb;
+  if (!items_dev || !block_prefix_dev || n_items < 1 || total_blocks < 1) return set_error("pack_batch: bad arguments");
+  pack_batch_kernel<<<total_blocks, 256, 0, (cudaStream_t)stream>>>((const PackItem*)items_dev, block_prefix_dev, n_items);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? 0 : set_cuda_error("pack_batch launch", e);
+}
 
 extern "C" int srb_pack_conv3x3_fwd(const float* w, int cout, int cin, int shuffle, float scale, void* wp,
                                     void* stream) {

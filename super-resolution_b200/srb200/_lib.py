@@ -50,6 +50,12 @@ class Wgrad3x3Args(C.Structure):
     ]
 
 
+class PackItem(C.Structure):
+    _fields_ = [("w", C.c_void_p), ("wp", C.c_void_p), ("cout", C.c_int), ("cin", C.c_int), ("ci_off", C.c_int),
+                ("n_out", C.c_int), ("flag", C.c_int), ("kind", C.c_int), ("kb_dst", C.c_int), ("kb_total", C.c_int),
+                ("scale", C.c_float), ("pad", C.c_int)]
+
+
 def sources():
     return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh")))
 
@@ -88,6 +94,7 @@ _SIGS = {
     "srb_pack_conv3x3_fwd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
     "srb_pack_conv3x3_dgrad": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                          C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "srb_pack_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "srb_wgrad3x3": (C.c_int, [C.POINTER(Wgrad3x3Args), C.c_void_p]),
     "srb_wgrad3x3_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "srb_conv_in_fwd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p,

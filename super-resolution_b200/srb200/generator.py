@@ -89,25 +89,55 @@ class GeneratorEngine:
             self._build_bwd_packs()
             self._packs_bwd_ready = True
 
+    # Packs are rebuilt after every optimizer step, so they go through ONE table-driven launch per direction
+    # (srb_pack_batch): the table (source / destination pointers and geometry of every pack item) is built once and
+    # reused for as long as the parameter storage and the pack buffers stay where they are.
+    def _upload_table(self, items, dev):
+        n = len(items)
+        arr = (L.PackItem * n)(*items)
+        raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(dev)
+        prefix, total = [], 0
+        for it in items:
+            prefix.append(total)
+            elems = 9 * it.cout * (it.cin if it.kind == 0 else it.n_out)
+            total += (elems + 255) // 256
+        pre = torch.tensor(prefix, dtype=torch.int32, device=dev)
+        return dict(raw=raw, prefix=pre, n=n, blocks=total)
+
+    def _run_table(self, tab) -> None:
+        L.check(L.lib().srb_pack_batch(tab["raw"].data_ptr(), tab["prefix"].data_ptr(), tab["n"], tab["blocks"], _st()),
+                "pack_batch")
+
+    def _ptr_key(self):
+        return (str(self._w("conv1").device),) + tuple(self._w(n).data_ptr() for n in self.names3x3)
+
     def _build_fwd_packs(self) -> None:
         dev = self._w("conv1").device
-        F_ = self.F
-        sizes = {}
-        total = 0
-        for n in self.names3x3:
-            w = self._w(n)
-            sizes[n] = (total, w.numel())
-            total += w.numel()
-        if getattr(self, "_fwd_flat", None) is None or self._fwd_flat.numel() != total or self._fwd_flat.device != dev:
+        key = self._ptr_key()
+        if getattr(self, "_fwd_tab_key", None) != key:
+            sizes, total = {}, 0
+            for n in self.names3x3:
+                w = self._w(n)
+                sizes[n] = (total, w.numel())
+                total += w.numel()
             self._fwd_flat = torch.empty(total, dtype=torch.bfloat16, device=dev)
-        self.wp: Dict[str, Tensor] = {}
-        self.bias_packed: Dict[str, Tensor] = {}
+            self.wp = {}
+            items = []
+            for n in self.names3x3:
+                off, cnt = sizes[n]
+                w = self._w(n)
+                if w.dtype != torch.float32 or not w.is_contiguous():
+                    raise RuntimeError("CUDA srb200: generator weights must be contiguous fp32")
+                self.wp[n] = self._fwd_flat[off:off + cnt]
+                items.append(L.PackItem(w.data_ptr(), self.wp[n].data_ptr(), w.shape[0], w.shape[1], 0, 0,
+                                        int(n.startswith("upsampling.")), 0, 0, 0, 1.0, 0))
+            self._fwd_tab = self._upload_table(items, dev)
+            self._fwd_tab_key = key
+        self._run_table(self._fwd_tab)
+        self.bias_packed = {}
         for n in self.names3x3:
-            off, cnt = sizes[n]
-            shuffle = n.startswith("upsampling.")
-            self.wp[n] = ops.pack_fwd(self._w(n), shuffle=shuffle, out=self._fwd_flat[off:off + cnt])
             b = self._b(n).detach()
-            if shuffle:
+            if n.startswith("upsampling."):
                 cout = b.numel()
                 idx = torch.arange(cout, device=dev)
                 b = b[4 * (idx % (cout // 4)) + idx // (cout // 4)].contiguous()
@@ -118,25 +148,39 @@ class GeneratorEngine:
         growth buffer [g_out(conv5), gz4, ..., gz_{jj+1}]; conv5's block is pre-scaled by the residual scale."""
         dev = self._w("conv1").device
         F_, kbF = self.F, self.F // 64
-        self.wd: Dict[str, Tensor] = {}
-        for i in range(self.nb):
-            for j in range(3):
-                s5 = DRB_SCALE * (self.rs if j == 2 else 1.0)
-                base = f"res_blocks.{i}.dense_blocks.{j}."
-                for jj in range(5):
-                    nsrc = 5 - jj
-                    pack = torch.empty(9 * nsrc * F_ * F_, dtype=torch.bfloat16, device=dev)
-                    for kk in range(5, jj, -1):           # forward conv kk feeds slot jj
-                        ops.pack_dgrad(self._w(base + f"b{kk}.0"), jj * F_, F_, pack, (5 - kk) * kbF, nsrc * kbF,
-                                       scale=s5 if kk == 5 else 1.0)
-                    self.wd[base + f"slot{jj}"] = pack
-        for n in ["conv2", "conv3.0"]:
-            pack = torch.empty(9 * F_ * F_, dtype=torch.bfloat16, device=dev)
-            self.wd[n] = ops.pack_dgrad(self._w(n), 0, F_, pack, 0, kbF)
-        for u in range(self.nup):
-            n = f"upsampling.{3 * u}"
-            pack = torch.empty(9 * 4 * F_ * F_, dtype=torch.bfloat16, device=dev)
-            self.wd[n] = ops.pack_dgrad(self._w(n), 0, F_, pack, 0, 4 * kbF, unshuffle=True)
+        key = self._ptr_key()
+        if getattr(self, "_bwd_tab_key", None) != key:
+            self.wd = {}
+            items = []
+
+            def item(name, ci_off, n_out, pack, kb_dst, kb_total, unshuffle=False, scale=1.0):
+                w = self._w(name)
+                items.append(L.PackItem(w.data_ptr(), pack.data_ptr(), w.shape[0], w.shape[1], ci_off, n_out,
+                                        int(unshuffle), 1, kb_dst, kb_total, float(scale), 0))
+
+            for i in range(self.nb):
+                for j in range(3):
+                    s5 = DRB_SCALE * (self.rs if j == 2 else 1.0)
+                    base = f"res_blocks.{i}.dense_blocks.{j}."
+                    for jj in range(5):
+                        nsrc = 5 - jj
+                        pack = torch.empty(9 * nsrc * F_ * F_, dtype=torch.bfloat16, device=dev)
+                        for kk in range(5, jj, -1):           # forward conv kk feeds slot jj
+                            item(base + f"b{kk}.0", jj * F_, F_, pack, (5 - kk) * kbF, nsrc * kbF,
+                                 scale=s5 if kk == 5 else 1.0)
+                        self.wd[base + f"slot{jj}"] = pack
+            for n in ["conv2", "conv3.0"]:
+                pack = torch.empty(9 * F_ * F_, dtype=torch.bfloat16, device=dev)
+                item(n, 0, F_, pack, 0, kbF)
+                self.wd[n] = pack
+            for u in range(self.nup):
+                n = f"upsampling.{3 * u}"
+                pack = torch.empty(9 * 4 * F_ * F_, dtype=torch.bfloat16, device=dev)
+                item(n, 0, F_, pack, 0, 4 * kbF, unshuffle=True)
+                self.wd[n] = pack
+            self._bwd_tab = self._upload_table(items, dev)
+            self._bwd_tab_key = key
+        self._run_table(self._bwd_tab)
 
     # ------------------------------------------------------------------ buffers
     def _get_bufs(self, B: int, h: int, w: int, training: bool, dev) -> _Bufs:
