@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=int(os.environ.get("SRB_BENCH_BATCH", 256)), help="per-GPU batch")
+    ap.add_argument("--batch", type=int, default=int(os.environ.get("SRB_BENCH_BATCH", 512)), help="per-GPU batch")
     ap.add_argument("--cpu-batch", type=int, default=16)
     ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying one CUDA graph")
     ap.add_argument("--no-extras", action="store_true", help="skip inference / generator-only / cpu_baseline legs")

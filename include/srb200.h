@@ -116,6 +116,11 @@ typedef struct srb_wgrad3x3_args {
 } srb_wgrad3x3_args;
 int srb_wgrad3x3(const srb_wgrad3x3_args* a, void* stream);
 size_t srb_wgrad3x3_workspace_bytes(int batch, int H, int W, int cin, int cout);
+/* Up to 8 weight gradients that share x, gy (different channel offsets), geometry, workspace and flags in ONE launch:
+ * the five convolutions of a DenseResidualBlock (models.py:24-32) read the same growth buffer and the same gradient
+ * buffer.  items[0].workspace must hold srb_wgrad3x3_group_workspace_bytes(...). */
+int srb_wgrad3x3_group(const srb_wgrad3x3_args* items, int n, void* stream);
+size_t srb_wgrad3x3_group_workspace_bytes(int batch, int H, int W, int n, const int* cin, const int* cout);
 
 /* ---- bandwidth-bound ends of the generator (csrc/gen_edge.cu) ------------------------------------
  * srb_conv_in_fwd : models.py:122-123  multiplier*x**power -> conv1; fp32 NCHW image -> PNHWC bf16 (two optional dsts)
@@ -201,6 +206,9 @@ int srb_ragan(const float* u, const float* v, int B, int n, float eps, float* lo
 int srb_gp_fwd(const float* g, int B, int n, float coef, float* norms, float* loss, void* stream);
 int srb_gp_bwd(const float* g, const float* norms, int B, int n, float coef, const float* gloss, float* gg,
                void* stream);
+
+/* Timing experiment aid: clock64 stamps of CTA 0's pipeline when srb_conv3x3 ran with flags bit 4 (tools/exp_conv.py). */
+int srb_igemm_read_stamps(long long* out16);
 
 /* Bring-up microbenchmark: sustained tcgen05.mma issue rate (csrc/probe.cu); not on the product path. */
 int srb_probe_mma_rate(int cta_group, int N, int iters, int a_row_shift, int mn_major, int b_lbo, int n_ctas,

@@ -2,6 +2,7 @@
 
 #include <mutex>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace srb {
@@ -17,6 +18,12 @@ int set_cuda_error(const char* what, cudaError_t e) {
   return 1;
 }
 const char* last_error() { return g_err; }
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("SRB_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
 
 int sm_count() {
   static int n = 0;

@@ -59,6 +59,9 @@ __device__ __forceinline__ void load_row64(const __nv_bfloat16* p, uint4 (&v)[8]
   for (int i = 0; i < 8; ++i) v[i] = __ldg(q + i);
 }
 
+// dbg bit 8: CTA 0 records clock64 stamps of its pipeline (tools/exp_conv.py reads them back)
+__device__ long long g_igemm_stamps[16];
+
 template <int MT>
 __global__ void __launch_bounds__(kIgemmThreads, 1)
 conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
@@ -79,6 +82,8 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const bool stamp = (p.dbg & 8) && blockIdx.x == 0;
+  if (stamp && threadIdx.x == 0) g_igemm_stamps[0] = clock64();
   // four accumulators (one per issuer warp) of 64 columns, double buffered: all 512 TMEM columns
   constexpr uint32_t kTmemCols = 512;
   constexpr int NACC = kIssuers / MT;           // accumulators that sum to one 128-row sub-tile
@@ -96,6 +101,9 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (stamp && threadIdx.x == 0) g_igemm_stamps[1] = clock64();
+  pdl_trigger();
+  pdl_wait();          // everything above overlapped the previous kernel; its results are visible from here on
 
   const int rows_per_tile = 128 * MT;
 
@@ -155,6 +163,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         const uint32_t d_tmem = tmem_base + as * 256 + iss * 64;
         for (int kb = 0; kb < p.KB; ++kb) {
           mbar_wait(&a_full[sa], pa, 4);
+          if (stamp && iss == 0 && kb == 0) g_igemm_stamps[work == (int)blockIdx.x ? 2 : 5] = clock64();
           const uint32_t a_lo = a0 + sa * a_stage16;
           uint32_t row16 = static_cast<uint32_t>(p.halo - p.pitch - 1) * 8u;     // tap (-1,-1), in 16-byte units
 #pragma unroll 1
@@ -177,6 +186,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
           }
           umma_commit(&a_empty[sa]);
           if (kb == p.KB - 1) umma_commit(&t_full[as]);
+          if (stamp && iss == 0 && kb == p.KB - 1) g_igemm_stamps[work == (int)blockIdx.x ? 3 : 6] = clock64();
           if (++sa == kAStages) { sa = 0; pa ^= 1; }
         }
         if (++as == 2) { as = 0; pt ^= 1; }
@@ -302,6 +312,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
       }
       tc_fence_before();
       __syncwarp();
+      if (stamp && warp == 5 && lane == 0) g_igemm_stamps[work == (int)blockIdx.x ? 4 : 7] = clock64();
       if (lane == 0) mbar_arrive(&t_empty[as]);
       if (++as == 2) { as = 0; pt ^= 1; }
     }
@@ -313,6 +324,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     tc_fence_after();
     tmem_dealloc(tmem_base, kTmemCols);
   }
+  if (stamp && threadIdx.x == 0) g_igemm_stamps[8] = clock64();
 }
 
 // ---------------------------------------------------------------------------------- host side
@@ -377,15 +389,20 @@ int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   if (MT == 2) {
     static bool attr2 = false;
     if (!attr2) { cudaFuncSetAttribute(conv3x3_igemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr2 = true; }
-    conv3x3_igemm_kernel<2><<<grid, kIgemmThreads, smem, stream>>>(tx, tw, p);
+    e = launch_pdl(conv3x3_igemm_kernel<2>, dim3(grid), dim3(kIgemmThreads), smem, stream, tx, tw, p);
   } else {
     static bool attr1 = false;
     if (!attr1) { cudaFuncSetAttribute(conv3x3_igemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr1 = true; }
-    conv3x3_igemm_kernel<1><<<grid, kIgemmThreads, smem, stream>>>(tx, tw, p);
+    e = launch_pdl(conv3x3_igemm_kernel<1>, dim3(grid), dim3(kIgemmThreads), smem, stream, tx, tw, p);
   }
-  e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return set_cuda_error("conv3x3_igemm launch", e);
   return 0;
 }
 
 }  // namespace srb
+
+extern "C" int srb_igemm_read_stamps(long long* out16) {
+  cudaError_t e = cudaMemcpyFromSymbol(out16, srb::g_igemm_stamps, sizeof(long long) * 16);
+  return e == cudaSuccess ? 0 : srb::set_cuda_error("read stamps", e);
+}

@@ -106,32 +106,47 @@ __global__ void conv_in_bwd_kernel(const float* __restrict__ img, int B, int Cim
 __device__ __forceinline__ float hardshrink(float v, float l) { return (v > l || v < -l) ? v : 0.f; }
 
 // one warp = one output pixel (all image channels, normally 1); lane = channel pair of the 64-wide input
-__global__ void conv_out_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_cstride, int x_coff, int B, int H, int W,
-                                    int F, const float* __restrict__ w, const float* __restrict__ bias, int Cimg,
-                                    float inv_multiplier, float power, float thres, int training,
-                                    float* __restrict__ out, float* __restrict__ srs, float* __restrict__ z) {
-  const int lane = threadIdx.x & 31;
-  const long long wid = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+__global__ void __launch_bounds__(256)
+conv_out_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_cstride, int x_coff, int B, int H, int W,
+                    int F, const float* __restrict__ w, const float* __restrict__ bias, int Cimg,
+                    float inv_multiplier, float power, float thres, int training,
+                    float* __restrict__ out, float* __restrict__ srs, float* __restrict__ z) {
+  // Eight lanes per output pixel, each lane owns 8 consecutive channels of every 64-channel block: one tap of one
+  // pixel is a single 128-byte row segment read with 16-byte loads (the 3x3 neighbourhood is re-read from L1/L2).
+  // Weights are staged once per block as fp32 [oc][t][c].
+  extern __shared__ float wsm[];
+  for (int i = threadIdx.x; i < Cimg * 9 * F; i += blockDim.x) {
+    const int c = i % F, t = (i / F) % 9, oc = i / (9 * F);
+    wsm[i] = w[(static_cast<size_t>(oc) * F + c) * 9 + t];
+  }
+  __syncthreads();
+  const int sub = threadIdx.x & 7;
+  const long long pix = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 3;
   const long long npix = 1LL * B * H * W;
-  if (wid >= npix) return;
-  const int px = int(wid % W); const int py = int((wid / W) % H); const int b = int(wid / (1LL * W * H));
+  const bool live = pix < npix;
+  const long long pc = live ? pix : npix - 1;
+  const int px = int(pc % W); const int py = int((pc / W) % H); const int b = int(pc / (1LL * W * H));
   const int pitch = W + 1;
   const long long row = (static_cast<long long>(b) * (H + 1) + py) * pitch + px;
   const long long R = 1LL * B * (H + 1) * pitch;
   for (int oc = 0; oc < Cimg; ++oc) {
     float acc = 0.f;
-    for (int c0 = lane * 2; c0 < F; c0 += 64) {
+    for (int c0 = sub * 8; c0 < F; c0 += 64) {
 #pragma unroll
       for (int t = 0; t < 9; ++t) {
         const long long rs = row + (t / 3 - 1) * pitch + (t % 3 - 1);
-        if (rs < 0 || rs >= R) continue;
-        const uint32_t v = *reinterpret_cast<const uint32_t*>(x + rs * x_cstride + x_coff + c0);
-        acc += bf16lo(v) * __ldg(w + (static_cast<size_t>(oc) * F + c0) * 9 + t) +
-               bf16hi(v) * __ldg(w + (static_cast<size_t>(oc) * F + c0 + 1) * 9 + t);
+        if (rs < 0 || rs >= R) continue;                 // zero rows / columns of PNHWC give the padding
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(x + rs * x_cstride + x_coff + c0));
+        const float4 w0 = *reinterpret_cast<const float4*>(wsm + (oc * 9 + t) * F + c0);
+        const float4 w1 = *reinterpret_cast<const float4*>(wsm + (oc * 9 + t) * F + c0 + 4);
+        acc += bf16lo(v.x) * w0.x + bf16hi(v.x) * w0.y + bf16lo(v.y) * w0.z + bf16hi(v.y) * w0.w +
+               bf16lo(v.z) * w1.x + bf16hi(v.z) * w1.y + bf16lo(v.w) * w1.z + bf16hi(v.w) * w1.w;
       }
     }
-    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0) {
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+    if (sub == 0 && live) {
       const float zz = (acc + bias[oc]) * inv_multiplier;
       const size_t oi = ((static_cast<size_t>(b) * Cimg + oc) * H + py) * W + px;
       if (z) z[oi] = zz;
@@ -330,8 +345,11 @@ extern "C" int srb_conv_out_fwd(const void* x, int x_cstride, int x_coff, int B,
                                 const float* bias, int Cimg, float multiplier, float power, float thres, int training,
                                 float* out, float* srs, float* z, void* stream) {
   if (F % 64) return set_error("conv_out: F must be a multiple of 64");
-  const long long threads = 1LL * B * H * W * 32;
-  conv_out_fwd_kernel<<<ceil_div(threads, 256), 256, 0, (cudaStream_t)stream>>>(
+  if ((x_cstride % 8) || (x_coff % 8)) return set_error("conv_out: channel stride/offset must keep 16-byte alignment");
+  const long long threads = 1LL * B * H * W * 8;
+  const size_t wsm = sizeof(float) * Cimg * 9 * F;
+  if (wsm > 48 * 1024) return set_error("conv_out: weights do not fit in shared memory");
+  conv_out_fwd_kernel<<<ceil_div(threads, 256), 256, wsm, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)x, x_cstride, x_coff, B, H, W, F, w, bias, Cimg, 1.f / multiplier, power, thres, training,
       out, srs, z);
   SRB_LAUNCH_CHECK("conv_out_fwd");

@@ -42,9 +42,19 @@ struct WgradParams {
   int unshuffle;
 };
 
+// Several weight gradients that read the same activation buffer and the same gradient buffer (the five convolutions of
+// a dense block) run as ONE launch: more work per CTA (fewer K splits, fewer partial tiles to reduce) and one
+// prologue / tail instead of five.
+constexpr int kWgMaxGroup = 8;
+struct WgradGroup {
+  int n, splits;
+  int unit_start[kWgMaxGroup + 1];   // first (cp, cb, dy) unit of every problem
+  WgradParams prob[kWgMaxGroup];
+};
+
 __global__ void __launch_bounds__(kWgThreads, 1)
 wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_g,
-                   const WgradParams p) {
+                   const __grid_constant__ WgradGroup g) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgStages * kWgStageBytes);
@@ -55,8 +65,12 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // decode work item
-  int w = blockIdx.x;
-  const int split = w % p.splits; w /= p.splits;
+  const int split = blockIdx.x % g.splits;
+  const int unit = blockIdx.x / g.splits;
+  int pi = 0;
+  while (pi + 1 < g.n && unit >= g.unit_start[pi + 1]) ++pi;
+  const WgradParams& p = g.prob[pi];
+  int w = unit - g.unit_start[pi];
   const int dyi = w % 3; w /= 3;                 // dy = dyi - 1
   const int cb = w % p.n_cb; w /= p.n_cb;
   const int cp = w;
@@ -80,6 +94,8 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -192,51 +208,39 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
 }
 
 // Sum the K splits, scale, and scatter to OIHW.  One thread per (t, ci, co); co fastest so workspace reads coalesce.
-__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, int cin, int cin_pad, int cout,
-                                    float alpha, int accumulate, int unshuffle, float* __restrict__ dw) {
-  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+// blockIdx.y selects the problem of the group.
+struct ReduceItem { const float* ws; float* dw; int cin, cin_pad, cout; float alpha; };
+struct ReduceGroup { int n, splits, accumulate, unshuffle; ReduceItem it[kWgMaxGroup]; };
+
+__global__ void wgrad_reduce_kernel(const __grid_constant__ ReduceGroup rg) {
+  const ReduceItem& r_ = rg.it[blockIdx.y];
+  const int cin = r_.cin, cout = r_.cout, cin_pad = r_.cin_pad;
   const long long total = 9LL * cin * cout;
-  if (idx >= total) return;
-  const int co = int(idx % cout);
-  long long r = idx / cout;
-  const int ci = int(r % cin);
-  const int t = int(r / cin);
-  float s = 0.f;
-  for (int sp = 0; sp < splits; ++sp) s += ws[((static_cast<size_t>(sp) * 9 + t) * cin_pad + ci) * cout + co];
-  s *= alpha;
-  const int cq = cout / 4;
-  const int co_dst = unshuffle ? (4 * (co % cq) + co / cq) : co;
-  float* d = dw + (static_cast<size_t>(co_dst) * cin + ci) * 9 + t;
-  *d = accumulate ? *d + s : s;
-}
-
-// dbias[co] = alpha * sum over all flat rows of gy[:, co]; one block per 64 channels... small and bandwidth-bound.
-__global__ void colsum_kernel(const __nv_bfloat16* __restrict__ g, int R, int cstride, int coff, int cout, float alpha,
-                              int accumulate, int unshuffle, float* __restrict__ dbias) {
-  // block = 256 threads = 8 row-lanes x 32 channel-pairs; grid.x = cout/64, grid.y = row slices
-  const int cpair = threadIdx.x & 31, rl = threadIdx.x >> 5;
-  const int c0 = blockIdx.x * 64 + cpair * 2;
-  float s0 = 0.f, s1 = 0.f;
-  for (long long q = blockIdx.y * 8 + rl; q < R; q += 8LL * gridDim.y) {
-    const uint32_t v = *reinterpret_cast<const uint32_t*>(g + q * cstride + coff + c0);
-    s0 += bf16lo(v); s1 += bf16hi(v);
-  }
-  __shared__ float red[8][64];
-  red[rl][cpair * 2] = s0; red[rl][cpair * 2 + 1] = s1;
-  __syncthreads();
-  if (threadIdx.x < 64) {
+  pdl_trigger();
+  pdl_wait();
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int co = int(idx % cout);
+    long long r = idx / cout;
+    const int ci = int(r % cin);
+    const int t = int(r / cin);
     float s = 0.f;
-    for (int i = 0; i < 8; ++i) s += red[i][threadIdx.x];
-    const int co = blockIdx.x * 64 + threadIdx.x;
+    for (int sp = 0; sp < rg.splits; ++sp) s += r_.ws[((static_cast<size_t>(sp) * 9 + t) * cin_pad + ci) * cout + co];
+    s *= r_.alpha;
     const int cq = cout / 4;
-    const int co_dst = unshuffle ? (4 * (co % cq) + co / cq) : co;
-    atomicAdd(dbias + co_dst, alpha * s);
+    const int co_dst = rg.unshuffle ? (4 * (co % cq) + co / cq) : co;
+    float* d = r_.dw + (static_cast<size_t>(co_dst) * cin + ci) * 9 + t;
+    *d = rg.accumulate ? *d + s : s;
   }
 }
 
-static void wgrad_plan(long long R, int cin, int cout, int* splits, int* chunks_per_split) {
-  const int n_cp = (cin + 127) / 128, n_cb = cout / 64;
-  const int units = n_cp * n_cb * 3;
+static void wgrad_group_plan(long long R, int n, const int* cin, const int* cout, int* splits, int* chunks_per_split,
+                             int* unit_start) {
+  int units = 0;
+  for (int i = 0; i < n; ++i) {
+    unit_start[i] = units;
+    units += ((cin[i] + 127) / 128) * (cout[i] / 64) * 3;
+  }
+  unit_start[n] = units;
   const int chunks = int((R + kWgKc - 1) / kWgKc);
   int s = sm_count() / units;                         // one CTA per SM (150 KB of smem each), one wave, no tail wave
   if (s < 1) s = 1;
@@ -248,48 +252,97 @@ static void wgrad_plan(long long R, int cin, int cout, int* splits, int* chunks_
   *splits = s; *chunks_per_split = cps;
 }
 
-int wgrad3x3_tc_launch(const srb_wgrad3x3_args* a, cudaStream_t stream) {
-  const int pitch = a->W + 1, P = (a->H + 1) * (a->W + 1);
-  const long long R = 1LL * a->batch * P;
+static size_t wgrad_group_ws(int n, const int* cin, const int* cout, int splits, size_t* offs) {
+  size_t total = 0;
+  for (int i = 0; i < n; ++i) {
+    if (offs) offs[i] = total;
+    total += static_cast<size_t>(splits) * 9 * ((cin[i] + 127) / 128) * 128 * cout[i];
+  }
+  return total * sizeof(float);
+}
+
+int wgrad3x3_tc_launch_group(const srb_wgrad3x3_args* a, int n, cudaStream_t stream) {
+  if (n < 1 || n > kWgMaxGroup) return set_error("wgrad3x3 group: 1..8 problems");
+  const srb_wgrad3x3_args& a0 = a[0];
+  const int pitch = a0.W + 1, P = (a0.H + 1) * (a0.W + 1);
+  const long long R = 1LL * a0.batch * P;
   if (R <= 0 || R > 0x7fffffffLL) return set_error("wgrad3x3: bad geometry");
-  if ((a->x_cstride % 8) || (a->gy_cstride % 8) || (a->x_coff % 8) || (a->gy_coff % 8))
-    return set_error("wgrad3x3: channel strides/offsets must keep 16-byte alignment");
+  int cin[kWgMaxGroup], cout[kWgMaxGroup];
+  for (int i = 0; i < n; ++i) {
+    const srb_wgrad3x3_args& ai = a[i];
+    if (ai.batch != a0.batch || ai.H != a0.H || ai.W != a0.W || ai.x != a0.x || ai.gy != a0.gy ||
+        ai.x_cstride != a0.x_cstride || ai.gy_cstride != a0.gy_cstride || ai.accumulate != a0.accumulate ||
+        ai.unshuffle != a0.unshuffle)
+      return set_error("wgrad3x3 group: problems must share buffers, geometry and flags");
+    if (ai.cin % 64 || ai.cout % 64 || !ai.dw) return set_error("wgrad3x3: channels must be multiples of 64");
+    if ((ai.x_cstride % 8) || (ai.gy_cstride % 8) || (ai.x_coff % 8) || (ai.gy_coff % 8))
+      return set_error("wgrad3x3: channel strides/offsets must keep 16-byte alignment");
+    cin[i] = ai.cin; cout[i] = ai.cout;
+  }
+  WgradGroup g{};
   int splits, cps;
-  wgrad_plan(R, a->cin, a->cout, &splits, &cps);
-  const int n_cp = (a->cin + 127) / 128, n_cb = a->cout / 64;
-  const size_t need = static_cast<size_t>(splits) * 9 * n_cp * 128 * a->cout * sizeof(float);
-  if (!a->workspace || a->workspace_bytes < need) return set_error("wgrad3x3: workspace too small");
+  wgrad_group_plan(R, n, cin, cout, &splits, &cps, g.unit_start);
+  size_t offs[kWgMaxGroup];
+  const size_t need = wgrad_group_ws(n, cin, cout, splits, offs);
+  if (!a0.workspace || a0.workspace_bytes < need) return set_error("wgrad3x3: workspace too small");
 
   CUtensorMap tx, tg;
-  if (make_tmap_2d_bf16(&tx, a->x, (uint64_t)a->x_cstride, (uint64_t)R, (uint64_t)a->x_cstride * 2, 64, kWgKc)) return 1;
-  if (make_tmap_2d_bf16(&tg, a->gy, (uint64_t)a->gy_cstride, (uint64_t)R, (uint64_t)a->gy_cstride * 2, 64, kWgGRows)) return 1;
+  if (make_tmap_2d_bf16(&tx, a0.x, (uint64_t)a0.x_cstride, (uint64_t)R, (uint64_t)a0.x_cstride * 2, 64, kWgKc)) return 1;
+  if (make_tmap_2d_bf16(&tg, a0.gy, (uint64_t)a0.gy_cstride, (uint64_t)R, (uint64_t)a0.gy_cstride * 2, 64, kWgGRows)) return 1;
 
-  WgradParams p{};
-  p.R = (int)R; p.pitch = pitch; p.cin = a->cin; p.cout = a->cout; p.n_cp = n_cp; p.n_cb = n_cb;
-  p.splits = splits; p.chunks_per_split = cps; p.x_coff = a->x_coff; p.gy_coff = a->gy_coff;
-  p.ws = (float*)a->workspace; p.base_offset_mode = a->flags & 1;
-  p.dbias = a->dbias; p.alpha = a->alpha; p.unshuffle = a->unshuffle;
-  if (a->dbias && !a->accumulate) cudaMemsetAsync(a->dbias, 0, sizeof(float) * a->cout, stream);
-
+  g.n = n; g.splits = splits;
+  ReduceGroup rg{};
+  rg.n = n; rg.splits = splits; rg.accumulate = a0.accumulate; rg.unshuffle = a0.unshuffle;
+  long long max_total = 0;
+  for (int i = 0; i < n; ++i) {
+    const srb_wgrad3x3_args& ai = a[i];
+    WgradParams& p = g.prob[i];
+    p.R = (int)R; p.pitch = pitch; p.cin = ai.cin; p.cout = ai.cout;
+    p.n_cp = (ai.cin + 127) / 128; p.n_cb = ai.cout / 64;
+    p.splits = splits; p.chunks_per_split = cps; p.x_coff = ai.x_coff; p.gy_coff = ai.gy_coff;
+    p.ws = (float*)a0.workspace + offs[i]; p.base_offset_mode = 0;
+    p.dbias = ai.dbias; p.alpha = ai.alpha; p.unshuffle = ai.unshuffle;
+    if (ai.dbias && !ai.accumulate) cudaMemsetAsync(ai.dbias, 0, sizeof(float) * ai.cout, stream);
+    rg.it[i] = ReduceItem{p.ws, ai.dw, ai.cin, p.n_cp * 128, ai.cout, ai.alpha};
+    const long long tot = 9LL * ai.cin * ai.cout;
+    if (tot > max_total) max_total = tot;
+  }
   static bool attr = false;
   const size_t smem = 1024 + size_t(kWgStages) * kWgStageBytes + 256;
   if (!attr) { cudaFuncSetAttribute(wgrad3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr = true; }
-  const int grid = n_cp * n_cb * 3 * splits;
-  wgrad3x3_tc_kernel<<<grid, kWgThreads, smem, stream>>>(tx, tg, p);
-  cudaError_t e = cudaGetLastError();
+  const int grid = g.unit_start[n] * splits;
+  cudaError_t e = launch_pdl(wgrad3x3_tc_kernel, dim3(grid), dim3(kWgThreads), smem, stream, tx, tg, g);
+  if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return set_cuda_error("wgrad3x3_tc launch", e);
-  const long long total = 9LL * a->cin * a->cout;
-  wgrad_reduce_kernel<<<ceil_div(total, 256), 256, 0, stream>>>(p.ws, splits, a->cin, n_cp * 128, a->cout, a->alpha,
-                                                                a->accumulate, a->unshuffle, a->dw);
-  e = cudaGetLastError();
+  int rblocks = ceil_div(max_total, 256);
+  const int cap = 2 * sm_count() / n > 1 ? 2 * sm_count() / n : 1;
+  if (rblocks > cap * 4) rblocks = cap * 4;
+  e = launch_pdl(wgrad_reduce_kernel, dim3(rblocks, n), dim3(256), 0, stream, rg);
+  if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return set_cuda_error("wgrad_reduce launch", e);
   return 0;
 }
 
+int wgrad3x3_tc_launch(const srb_wgrad3x3_args* a, cudaStream_t stream) { return wgrad3x3_tc_launch_group(a, 1, stream); }
+
 }  // namespace srb
 
 extern "C" size_t srb_wgrad3x3_workspace_bytes(int batch, int H, int W, int cin, int cout) {
-  int splits, cps;
-  srb::wgrad_plan(1LL * batch * (H + 1) * (W + 1), cin, cout, &splits, &cps);
-  return static_cast<size_t>(splits) * 9 * ((cin + 127) / 128) * 128 * cout * sizeof(float);
+  int splits, cps, us[srb::kWgMaxGroup + 1];
+  srb::wgrad_group_plan(1LL * batch * (H + 1) * (W + 1), 1, &cin, &cout, &splits, &cps, us);
+  return srb::wgrad_group_ws(1, &cin, &cout, splits, nullptr);
+}
+
+extern "C" size_t srb_wgrad3x3_group_workspace_bytes(int batch, int H, int W, int n, const int* cin, const int* cout) {
+  if (n < 1 || n > srb::kWgMaxGroup) return 0;
+  int splits, cps, us[srb::kWgMaxGroup + 1];
+  srb::wgrad_group_plan(1LL * batch * (H + 1) * (W + 1), n, cin, cout, &splits, &cps, us);
+  return srb::wgrad_group_ws(n, cin, cout, splits, nullptr);
+}
+
+extern "C" int srb_wgrad3x3_group(const srb_wgrad3x3_args* items, int n, void* stream) {
+  if (!items) return srb::set_error("wgrad3x3 group: null pointer");
+  for (int i = 0; i < n; ++i)
+    if (!items[i].x || !items[i].gy || !items[i].dw) return srb::set_error("wgrad3x3 group: null pointer");
+  return srb::wgrad3x3_tc_launch_group(items, n, (cudaStream_t)stream);
 }

@@ -96,6 +96,8 @@ _SIGS = {
                                          C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "srb_pack_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "srb_wgrad3x3": (C.c_int, [C.POINTER(Wgrad3x3Args), C.c_void_p]),
+    "srb_wgrad3x3_group": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "srb_wgrad3x3_group_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "srb_wgrad3x3_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "srb_conv_in_fwd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p,
                                   C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
@@ -144,6 +146,7 @@ _SIGS = {
                             C.c_void_p]),
     "srb_gp_fwd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
     "srb_gp_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "srb_igemm_read_stamps": (C.c_int, [C.c_void_p]),
     "srb_probe_mma_rate": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                      C.c_void_p]),
 }

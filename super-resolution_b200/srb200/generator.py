@@ -216,6 +216,7 @@ class GeneratorEngine:
             for (hh, ww, cin, cout) in ([(h, w, k * F_, F_) for k in range(1, 6)]
                                         + [(h << u, w << u, F_, 4 * F_) for u in range(self.nup)] + [(H, W, F_, F_)]):
                 ws = max(ws, ops.wgrad_workspace_bytes(B, hh, ww, cin, cout))
+            ws = max(ws, ops.wgrad_group_workspace_bytes(B, h, w, [k * F_ for k in range(1, 6)], [F_] * 5))
             bf.ws = torch.empty(ws, dtype=torch.uint8, device=dev)
             gp = [(n, p) for n, p in self.p.items() if n not in ("power", "multiplier")]
             bf.gflat = torch.zeros(sum(p.numel() for _, p in gp), device=dev)
@@ -373,9 +374,14 @@ class GeneratorEngine:
                 else:
                     self._dconv(G, 5 * F_, self.wd[base + "slot0"], bf.g_out1, 0, F_, res1=(G, 0, sid),
                                 res2=(bf.G[2], 0, 1.0))
-                for k in range(1, 6):
-                    self._wgrad(bf, gb, k * F_, G, (5 - k) * F_ if k < 5 else 0, F_, base + f"b{k}.0",
-                                alpha=s5 if k == 5 else 1.0)
+                if self.impl == L.IMPL_TCGEN05:      # the block's five weight gradients in one launch
+                    ops.wgrad3x3_group(gb, G, [(0, k * F_, (5 - k) * F_ if k < 5 else 0, F_,
+                                                bf.grads[base + f"b{k}.0.weight"], bf.grads[base + f"b{k}.0.bias"],
+                                                s5 if k == 5 else 1.0) for k in range(1, 6)], bf.ws)
+                else:
+                    for k in range(1, 6):
+                        self._wgrad(bf, gb, k * F_, G, (5 - k) * F_ if k < 5 else 0, F_, base + f"b{k}.0",
+                                    alpha=s5 if k == 5 else 1.0)
             hook(f"res_blocks.{i}.dense_blocks.0.b1.0.weight")
         # conv1 (models.py:63,122-123): weight gradient from g_out1 + g_s
         L.check(lib.srb_conv_in_bwd(img.data_ptr(), B, ch, h, w, sv["multiplier"], sv["power"], bf.g_out1.data_ptr(),

@@ -150,6 +150,35 @@ def wgrad3x3(x: Tensor, x_coff: int, cin: int, gy: Tensor, gy_coff: int, cout: i
         L.check(L.lib().srb_wgrad3x3(C.byref(a), _stream()), "wgrad3x3")
 
 
+def wgrad_group_workspace_bytes(batch: int, H: int, W: int, cins, couts) -> int:
+    n = len(cins)
+    ci = (C.c_int * n)(*cins)
+    co = (C.c_int * n)(*couts)
+    return int(L.lib().srb_wgrad3x3_group_workspace_bytes(batch, H, W, n, C.cast(ci, C.c_void_p), C.cast(co, C.c_void_p)))
+
+
+def wgrad3x3_group(x: Tensor, gy: Tensor, problems, workspace: Tensor, *, accumulate: bool = False) -> None:
+    """Several weight gradients over the same buffers in one launch.  ``problems`` = list of
+    (x_coff, cin, gy_coff, cout, dw, dbias_or_None, alpha)."""
+    _require_cuda(x, "wgrad3x3_group")
+    B, Hp, Wp, Cx = x.shape
+    assert gy.shape[:3] == x.shape[:3]
+    n = len(problems)
+    arr = (L.Wgrad3x3Args * n)()
+    flops = 0.0
+    for a, (x_coff, cin, gy_coff, cout, dw, db, alpha) in zip(arr, problems):
+        assert dw.dtype == torch.float32 and dw.is_contiguous() and tuple(dw.shape) == (cout, cin, 3, 3)
+        a.batch, a.H, a.W = B, Hp - 1, Wp - 1
+        a.x, a.x_cstride, a.x_coff, a.cin = x.data_ptr(), Cx, x_coff, cin
+        a.gy, a.gy_cstride, a.gy_coff, a.cout = gy.data_ptr(), gy.shape[-1], gy_coff, cout
+        a.dw, a.dbias, a.alpha = dw.data_ptr(), _ptr(db), alpha
+        a.accumulate, a.unshuffle = int(accumulate), 0
+        a.workspace, a.workspace_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+        flops += 2.0 * B * a.H * a.W * 9 * cin * cout
+    with _Prof("wgrad3x3", flops):
+        L.check(L.lib().srb_wgrad3x3_group(C.cast(arr, C.c_void_p), n, _stream()), "wgrad3x3_group")
+
+
 def read_fault() -> int:
     v = C.c_uint(0)
     L.check(L.lib().srb_read_fault(C.byref(v)), "read_fault")

@@ -97,7 +97,8 @@ def test_training_grads_match_golden_and_oracle(golden):
         assert (a[:64] - h).abs().max().item() <= 0.2 * b.abs().max().item() + 1e-12
 
 
-@pytest.mark.parametrize("batch,lr_size,nup,nb", [(3, 20, 2, 1), (130, 20, 2, 1), (5, 13, 1, 2)])
+@pytest.mark.parametrize("batch,lr_size,nup,nb", [(3, 20, 2, 1), (130, 20, 2, 1), (5, 13, 1, 2),
+                                                  (4, 10, 3, 2), (2, 40, 1, 1)])   # x8 (config 4) and x2 (default.json)
 def test_forward_backward_vs_oracle_shapes(batch, lr_size, nup, nb):
     """covers MT=1 and MT=2 tile paths, odd widths, and a second RRDB (outer skip in backward)."""
     dev = _dev()
