@@ -73,6 +73,31 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64
   return 0;
 }
 
+int make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint32_t box[4]) {
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) return set_error("cuTensorMapEncodeTiled entry point not available");
+  const uint64_t inner_bytes = dims[0] * 2, box_bytes = uint64_t(box[0]) * 2;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (inner_bytes & 15))
+    return set_error("tensor map: base and innermost extent must be 16-byte aligned");
+  if (box[0] > dims[0] || (box_bytes != 32 && box_bytes != 64 && box_bytes != 128))
+    return set_error("tensor map (4d): innermost box must be 16, 32 or 64 bf16");
+  cuuint64_t d[4] = {dims[0], dims[1], dims[2], dims[3]};
+  cuuint64_t strides[3] = {inner_bytes, inner_bytes * dims[1], inner_bytes * dims[1] * dims[2]};
+  cuuint32_t b[4] = {box[0], box[1], box[2], box[3]};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUtensorMapSwizzle sw = box_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
+                              : box_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), d, strides, b, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[128];
+    snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled (4d) failed with CUresult %d", int(r));
+    return set_error(buf);
+  }
+  return 0;
+}
+
 const char* last_error();
 
 }  // namespace srb

@@ -18,6 +18,9 @@ int sm_count();
 // out-of-bounds elements read as zero.  Returns 0 on success.
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t row_stride_bytes,
                       uint32_t box_inner, uint32_t box_outer);
+// 4-D tiled map over a dense bf16 [d3][d2][d1][d0] tensor (d0 innermost; the box takes 16/32/64 of its elements);
+// swizzle = the innermost box extent in bytes (32B/64B/128B), out-of-bounds elements read as zero.
+int make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint32_t box[4]);
 
 inline int ceil_div(long long a, long long b) { return int((a + b - 1) / b); }
 

@@ -14,7 +14,11 @@
 //                                  epi: bias, LeakyReLU, or multiply by LeakyReLU'(ref) (the mask of the layer below)
 //   dmma_wgrad_kernel<KS,MT>       dW[co][ci][t] += sum_pixels gz[p][co] * a[p*s + t][ci];  db[co] += sum gz
 //   dl1_* kernels                  the 1-channel image end of the stack (Cin = 1) on CUDA cores in fp32
+#include <math.h>
+#include <string.h>
+
 #include "common.cuh"
+#include "sm100.cuh"
 
 namespace srb {
 
@@ -57,28 +61,45 @@ struct DmmaConvP {
   int cin, cout;               // real channel counts (<= KS*16, <= NT*8)
   int stride;                  // MODE 0
   int TH, IMGS;                // tile = IMGS images x TH rows (MODE 0: destination rows; MODE 1: phase-grid rows)
+  int nst, tile_bytes;         // ring of nst source-tile buffers, tile_bytes apart (multiple of 1024)
   int tiles_y, n_tiles;
   int act;                     // 0 none, 1 LeakyReLU(slope), 2 multiply by (ref > 0 ? 1 : slope)
   float slope;
 };
 
 constexpr int kDmmaThreads = 256;
+constexpr int kDmmaMaxStages = 4;
 
+// Source tiles arrive by TMA: one 4-D box [IMGS][TR][TC][cin] per tile (halo included, zero-filled outside the image
+// and past the last image), dense in shared memory with the hardware swizzle of the pixel size (32/64/128 B), which
+// keeps the ldmatrix reads of 8 neighbouring pixels conflict-free.  p.nst tile buffers form a ring: the load of tile
+// i + nst - 1 is issued when tile i - 1 has been consumed.
 template <int KS, int NT, int MODE>
 __global__ void __launch_bounds__(kDmmaThreads)
-dmma_conv_kernel(const DmmaConvP p) {
-  constexpr int PP = KS * 32 + 16;                    // bytes per pixel row in shared memory (16 B skew: conflict-free ldmatrix)
+dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
+  constexpr int PP = KS * 32 + 16;                    // weight row pitch (16 B skew: conflict-free ldmatrix)
+  constexpr int P = KS * 32;                          // source pixel pitch (swizzled)
+  constexpr int SH = KS == 1 ? 2 : KS == 2 ? 1 : 0;   // swizzle: 16-byte chunk index ^= (pixel >> SH) & SWM
+  constexpr int SWM = 2 * KS - 1;
   constexpr int NROWS = NT * 8;
-  extern __shared__ __align__(16) uint8_t dsm[];
-  uint8_t* w_s = dsm;
-  uint8_t* in_s = dsm + 9 * NROWS * PP;
+  extern __shared__ __align__(1024) uint8_t dsm[];
+  uint8_t* in_s0 = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dsm) + 1023) & ~uintptr_t(1023));
+  uint8_t* w_s = in_s0 + p.nst * p.tile_bytes;
+  uint8_t* stage_s = w_s + 9 * NROWS * PP;                       // per-warp epilogue staging (NT >= 2)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stage_s + (NT >= 2 ? (kDmmaThreads / 32) * 32 * (NT * 16 + 16) : 0));
   const int S = MODE == 0 ? p.stride : 1;
   const int Wg = MODE == 0 ? p.Wd : p.Wd / 2;         // width of the fragment grid (destination or phase grid)
   const int Hg = MODE == 0 ? p.Hd : p.Hd / 2;
   const int TR = MODE == 0 ? p.TH * S + 2 : p.TH + 1;
   const int TC = MODE == 0 ? Wg * S + 2 : Wg + 1;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool tma = p.in_f32 == nullptr;
 
+  if (threadIdx.x == 0 && tma) {
+    tma_prefetch_desc(&tmap);
+    for (int i = 0; i < p.nst; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+  }
   // weights -> shared memory (once per CTA)
   {
     constexpr int CH = KS * 2;                        // 16-byte chunks per row
@@ -94,37 +115,52 @@ dmma_conv_kernel(const DmmaConvP p) {
   const int npair = (nfrag + 1) >> 1;
   constexpr int NPH = MODE == 0 ? 1 : 4;
 
-  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-    const int ty = tile % p.tiles_y;
-    const int img0 = (tile / p.tiles_y) * p.IMGS;
-    const int y0 = ty * p.TH;                         // first fragment-grid row of the tile
-    __syncthreads();                                  // previous tile fully consumed (and weights visible)
-    // ---- stage the zero-padded source tile
-    {
+  auto load_tile = [&](int tile, int slot) {
+    const int ty_ = tile % p.tiles_y;
+    const int img0_ = (tile / p.tiles_y) * p.IMGS;
+    const int gy0 = MODE == 0 ? ty_ * p.TH * S - 1 : ty_ * p.TH;
+    const int gx0 = MODE == 0 ? -1 : 0;
+    uint8_t* dst = in_s0 + slot * p.tile_bytes;
+    if (tma) {
+      if (threadIdx.x == 0) {
+        mbar_expect_tx(&bars[slot], static_cast<uint32_t>(p.IMGS * TR * TC * P));
+        tma_load_4d(dst, &tmap, 0, gx0, gy0, img0_, &bars[slot]);
+      }
+    } else {                                          // single fp32 channel (tiny layers): convert on the way in
       constexpr int CH = KS * 2;
       const int total = p.IMGS * TR * TC * CH;
-      const int gy0 = MODE == 0 ? y0 * S - 1 : y0;
-      const int gx0 = MODE == 0 ? -1 : 0;
       for (int i = threadIdx.x; i < total; i += kDmmaThreads) {
-        const int c = i % CH;
-        int r = i / CH;
+        const int n = i / CH, c = i - n * CH;
+        int r = n;
         const int tc = r % TC; r /= TC;
         const int tr = r % TR;
         const int im = r / TR;
-        const int gy = gy0 + tr, gx = gx0 + tc, b = img0 + im;
+        const int gy = gy0 + tr, gx = gx0 + tc, b = img0_ + im;
         uint4 v = make_uint4(0, 0, 0, 0);
-        if (b < p.B && gy >= 0 && gy < p.Hs && gx >= 0 && gx < p.Ws) {
-          const size_t pix = (static_cast<size_t>(b) * p.Hs + gy) * p.Ws + gx;
-          if (p.in_f32) {
-            if (c == 0) v.x = dpack_bf16(__ldg(p.in_f32 + pix), 0.f);
-          } else if (c * 8 < p.cin) {
-            v = __ldg(reinterpret_cast<const uint4*>(p.in + pix * p.cin) + c);
-          }
-        }
-        *reinterpret_cast<uint4*>(in_s + ((im * TR + tr) * TC + tc) * PP + c * 16) = v;
+        if (c == 0 && b < p.B && gy >= 0 && gy < p.Hs && gx >= 0 && gx < p.Ws)
+          v.x = dpack_bf16(__ldg(p.in_f32 + (static_cast<size_t>(b) * p.Hs + gy) * p.Ws + gx), 0.f);
+        *reinterpret_cast<uint4*>(dst + n * P + ((c ^ ((n >> SH) & SWM)) << 4)) = v;
       }
     }
-    __syncthreads();
+  };
+  __syncthreads();                                    // barriers initialised (weights: covered by the loop's barrier)
+  for (int k = 0; k < p.nst - 1; ++k) {
+    const int t = blockIdx.x + k * gridDim.x;
+    if (t < p.n_tiles) load_tile(t, k);
+  }
+  int k = 0;
+  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++k) {
+    const int ty = tile % p.tiles_y;
+    const int img0 = (tile / p.tiles_y) * p.IMGS;
+    const int y0 = ty * p.TH;                         // first fragment-grid row of the tile
+    const int slot = k % p.nst;
+    __syncthreads();                                  // tile k-1 fully consumed: its buffer takes tile k + nst - 1
+    {
+      const int t = tile + (p.nst - 1) * gridDim.x;
+      if (t < p.n_tiles) load_tile(t, (k + p.nst - 1) % p.nst);
+    }
+    if (tma) mbar_wait(&bars[slot], (k / p.nst) & 1, 0x30);
+    const uint32_t tile_u32 = dsmem_u32(in_s0 + slot * p.tile_bytes);
 
     for (int it = warp; it < NPH * npair; it += kDmmaThreads / 32) {
       const int ph = MODE == 0 ? 0 : it / npair;
@@ -137,8 +173,8 @@ dmma_conv_kernel(const DmmaConvP p) {
         for (int n = 0; n < NT; ++n)
 #pragma unroll
           for (int i = 0; i < 4; ++i) acc[f][n][i] = 0.f;
-      // per-lane ldmatrix row base for the two fragments
-      uint32_t abase[2];
+      // per-lane tile pixel (at tap 0,0) of the fragment row this lane addresses, for the two fragments
+      int nbase[2];
 #pragma unroll
       for (int f = 0; f < 2; ++f) {
         int m = (pr * 2 + f) * 16 + (lane & 15);
@@ -146,8 +182,9 @@ dmma_conv_kernel(const DmmaConvP p) {
         const int im = m / M_img;
         const int rem = m - im * M_img;
         const int yl = rem / Wg, x = rem - yl * Wg;
-        abase[f] = dsmem_u32(in_s) + ((im * TR + yl * S) * TC + x * S) * PP + (lane >> 4) * 16;
+        nbase[f] = (im * TR + yl * S) * TC + x * S;
       }
+      const int hi = lane >> 4;
       const bool two = (pr * 2 + 1) < nfrag;
       const uint32_t wlane = dsmem_u32(w_s) + ((lane & 7) + ((lane >> 4) << 3)) * PP + ((lane >> 3) & 1) * 16;
       const uint32_t wlane2 = dsmem_u32(w_s) + (lane & 7) * PP + ((lane >> 3) & 1) * 16;   // x2 form (NT == 1)
@@ -157,15 +194,18 @@ dmma_conv_kernel(const DmmaConvP p) {
 #pragma unroll
         for (int kx = 0; kx < 3; ++kx) {
           if (MODE == 1 && ((kx ^ px) & 1) == 0) continue;
-          int toff;
-          if (MODE == 0) toff = (ky * TC + kx) * PP;
-          else toff = (((py == 1 && ky == 0) ? TC : 0) + ((px == 1 && kx == 0) ? 1 : 0)) * PP;
+          int noff;
+          if (MODE == 0) noff = ky * TC + kx;
+          else noff = ((py == 1 && ky == 0) ? TC : 0) + ((px == 1 && kx == 0) ? 1 : 0);
           const int wt = (ky * 3 + kx) * NROWS * PP;
+          const int n0 = nbase[0] + noff, n1 = nbase[1] + noff;
+          const uint32_t row0 = tile_u32 + n0 * P, row1 = tile_u32 + n1 * P;
+          const int sw0 = (n0 >> SH) & SWM, sw1 = (n1 >> SH) & SWM;
 #pragma unroll
           for (int kk = 0; kk < KS; ++kk) {
             uint32_t a0[4], a1[4];
-            ldsm_x4(abase[0] + toff + kk * 32, a0);
-            if (two) ldsm_x4(abase[1] + toff + kk * 32, a1);
+            ldsm_x4(row0 + (((kk * 2 + hi) ^ sw0) << 4), a0);
+            if (two) ldsm_x4(row1 + (((kk * 2 + hi) ^ sw1) << 4), a1);
             if (NT == 1) {
               uint32_t b0, b1;
               ldsm_x2(wlane2 + wt + kk * 32, b0, b1);
@@ -187,8 +227,71 @@ dmma_conv_kernel(const DmmaConvP p) {
           }
         }
       }
-      // ---- epilogue: rows g and g+8 of each fragment, columns nt*8 + 2t, +1
       const int g = lane >> 2, t2 = (lane & 3) * 2;
+      if constexpr (NT >= 2) {
+        // ---- epilogue through a per-warp staging tile: fragments are scattered 4-byte pieces, global memory wants
+        // whole pixel rows.  Values go to shared memory as bf16 [32 rows][COUT] (+16 B skew), then each lane moves
+        // 16-byte chunks: consecutive lanes cover consecutive channels of consecutive pixels (coalesced stores and,
+        // for the mask epilogue, coalesced reads of the reference activation).
+        constexpr int SP = NT * 16 + 16;
+        uint8_t* stg = stage_s + warp * (32 * SP);
+        // destination pixel of staging row `lane` (-1: nothing to store)
+        long long mypix = -1;
+        {
+          const int m = pr * 32 + lane;
+          if (m < M && (lane < 16 || two)) {
+            const int im = m / M_img;
+            const int rem = m - im * M_img;
+            const int yl = rem / Wg, x = rem - yl * Wg;
+            const int b = img0 + im, yg = y0 + yl;
+            if (b < p.B && yg < Hg) {
+              const int yd = MODE == 0 ? yg : 2 * yg + py;
+              const int xd = MODE == 0 ? x : 2 * x + px;
+              mypix = (static_cast<long long>(b) * p.Hd + yd) * p.Wd + xd;
+            }
+          }
+        }
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+#pragma unroll
+          for (int hrow = 0; hrow < 2; ++hrow) {
+            const int r = f * 16 + g + hrow * 8;
+#pragma unroll
+            for (int n = 0; n < NT; ++n) {
+              const int col = n * 8 + t2;
+              float v0 = acc[f][n][hrow * 2], v1 = acc[f][n][hrow * 2 + 1];
+              if (p.bias) { v0 += __ldg(p.bias + col); v1 += __ldg(p.bias + col + 1); }
+              if (p.act == 1) {
+                v0 = v0 > 0.f ? v0 : v0 * p.slope;
+                v1 = v1 > 0.f ? v1 : v1 * p.slope;
+              }
+              *reinterpret_cast<uint32_t*>(stg + r * SP + col * 2) = dpack_bf16(v0, v1);
+            }
+          }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < NT; ++i) {
+          const int c = lane + 32 * i;
+          const int r = c / NT, part = c - r * NT;
+          const long long pix = __shfl_sync(0xffffffffu, mypix, r);
+          if (pix < 0) continue;
+          uint4 v = *reinterpret_cast<const uint4*>(stg + r * SP + part * 16);
+          if (p.act == 2) {
+            const uint4 m4 = __ldg(reinterpret_cast<const uint4*>(p.ref + pix * p.cout) + part);
+            const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
+            uint32_t vw[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              vw[q] = dpack_bf16(dbf_lo(vw[q]) * (dbf_lo(mw[q]) > 0.f ? 1.f : p.slope),
+                                 dbf_hi(vw[q]) * (dbf_hi(mw[q]) > 0.f ? 1.f : p.slope));
+            v = make_uint4(vw[0], vw[1], vw[2], vw[3]);
+          }
+          *(reinterpret_cast<uint4*>(p.out + pix * p.cout) + part) = v;
+        }
+        __syncwarp();
+      } else {
+      // ---- direct epilogue (single output channel): rows g and g+8 of each fragment, columns nt*8 + 2t, +1
 #pragma unroll
       for (int f = 0; f < 2; ++f) {
         if (f == 1 && !two) break;
@@ -234,6 +337,7 @@ dmma_conv_kernel(const DmmaConvP p) {
           }
         }
       }
+      }
     }
   }
 }
@@ -248,26 +352,47 @@ struct DmmaWgradP {
   int B, Hi, Wi, Ho, Wo, cin, cout, stride;
   int co_off;                  // first output channel handled by this launch (MT*16 channels from there)
   int TH, IMGS, tiles_y, n_tiles;
+  int nst, a_bytes, g_bytes;   // ring of nst stages; activation / gradient tile sizes (multiples of 1024)
 };
 
 constexpr int kDwgThreads = 288;   // nine warps: one per filter tap
+constexpr int kDwgMaxStages = 3;
 
+// Both operand tiles arrive by TMA into a ring of p.nst stages (see dmma_conv_kernel): the activation tile with its
+// halo as a [IMGS][TR][TC][cin] box, the gradient tile as a [IMGS][TH][Wo][MT*16] box whose rows are the fragment-row
+// index m; both dense with the hardware swizzle of their pixel size.
 template <int KS, int MT>
 __global__ void __launch_bounds__(kDwgThreads)
-dmma_wgrad_kernel(const DmmaWgradP p) {
-  constexpr int PPA = KS * 32 + 16;
-  constexpr int PPG = MT * 32 + 16;
+dmma_wgrad_kernel(const DmmaWgradP p, const __grid_constant__ CUtensorMap tmap_a,
+                  const __grid_constant__ CUtensorMap tmap_g) {
+  constexpr int PA = KS * 32, PG = MT * 32;
+  constexpr int SHA = KS == 1 ? 2 : KS == 2 ? 1 : 0, SWA = 2 * KS - 1;
+  constexpr int SHG = MT == 1 ? 2 : MT == 2 ? 1 : 0, SWG = 2 * MT - 1;
   constexpr int NT = KS * 2;
-  extern __shared__ __align__(16) uint8_t dsm[];
+  extern __shared__ __align__(1024) uint8_t dsm[];
+  uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dsm) + 1023) & ~uintptr_t(1023));
+  const int stage_bytes = p.a_bytes + p.g_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + p.nst * stage_bytes);
   const int S = p.stride;
   const int TR = p.TH * S + 2, TC = p.Wo * S + 2;
   const int M_img = p.TH * p.Wo;
   const int M = p.IMGS * M_img;
   const int M16 = (M + 15) & ~15;
-  uint8_t* a_s = dsm;
-  uint8_t* g_s = dsm + p.IMGS * TR * TC * PPA;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ky = warp / 3, kx = warp - ky * 3;
+  const bool g_tma = p.gz_f32 == nullptr;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmap_a);
+    if (g_tma) tma_prefetch_desc(&tmap_g);
+    for (int i = 0; i < p.nst; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+  }
+  // fragment rows M .. M16-1 of every gradient buffer stay zero (TMA never writes them)
+  for (int i = threadIdx.x; i < p.nst * (M16 - M) * (PG / 16); i += kDwgThreads) {
+    const int st = i / ((M16 - M) * (PG / 16)), r = i - st * ((M16 - M) * (PG / 16));
+    *reinterpret_cast<uint4*>(ring + st * stage_bytes + p.a_bytes + M * PG + r * 16) = make_uint4(0, 0, 0, 0);
+  }
 
   float acc[MT][NT][4];
 #pragma unroll
@@ -276,56 +401,58 @@ dmma_wgrad_kernel(const DmmaWgradP p) {
     for (int n = 0; n < NT; ++n)
 #pragma unroll
       for (int i = 0; i < 4; ++i) acc[m][n][i] = 0.f;
-  float dbacc = 0.f;
+  float db0 = 0.f, db1 = 0.f;
 
-  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-    const int ty = tile % p.tiles_y;
-    const int img0 = (tile / p.tiles_y) * p.IMGS;
-    const int y0 = ty * p.TH;
-    __syncthreads();
-    {  // input tile with halo
-      constexpr int CH = KS * 2;
-      const int total = p.IMGS * TR * TC * CH;
-      for (int i = threadIdx.x; i < total; i += kDwgThreads) {
-        const int c = i % CH;
-        int r = i / CH;
-        const int tc = r % TC; r /= TC;
-        const int tr = r % TR;
-        const int im = r / TR;
-        const int gy = y0 * S - 1 + tr, gx = tc - 1, b = img0 + im;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (b < p.B && gy >= 0 && gy < p.Hi && gx >= 0 && gx < p.Wi && c * 8 < p.cin)
-          v = __ldg(reinterpret_cast<const uint4*>(p.a + ((static_cast<size_t>(b) * p.Hi + gy) * p.Wi + gx) * p.cin) + c);
-        *reinterpret_cast<uint4*>(a_s + ((im * TR + tr) * TC + tc) * PPA + c * 16) = v;
-      }
+  auto load_tile = [&](int tile, int slot) {
+    const int ty_ = tile % p.tiles_y;
+    const int img0_ = (tile / p.tiles_y) * p.IMGS;
+    const int y0_ = ty_ * p.TH;
+    uint8_t* a_dst = ring + slot * stage_bytes;
+    uint8_t* g_dst = a_dst + p.a_bytes;
+    if (threadIdx.x == 0) {
+      mbar_expect_tx(&bars[slot], static_cast<uint32_t>(p.IMGS * TR * TC * PA + (g_tma ? M * PG : 0)));
+      tma_load_4d(a_dst, &tmap_a, 0, -1, y0_ * S - 1, img0_, &bars[slot]);
+      if (g_tma) tma_load_4d(g_dst, &tmap_g, p.co_off, 0, y0_, img0_, &bars[slot]);
     }
-    {  // gradient tile, rows = fragment-row index m (zero beyond the valid pixels)
+    if (!g_tma) {                                      // single fp32 gradient channel (last layer): convert on the way in
       constexpr int CH = MT * 2;
-      for (int i = threadIdx.x; i < M16 * CH; i += kDwgThreads) {
-        const int c = i % CH, m = i / CH;
+      for (int i = threadIdx.x; i < M * CH; i += kDwgThreads) {
+        const int m = i / CH, c = i - m * CH;
+        const int im = m / M_img;
+        const int rem = m - im * M_img;
+        const int yl = rem / p.Wo, x = rem - yl * p.Wo;
+        const int b = img0_ + im, y = y0_ + yl;
         uint4 v = make_uint4(0, 0, 0, 0);
-        if (m < M) {
-          const int im = m / M_img;
-          const int rem = m - im * M_img;
-          const int yl = rem / p.Wo, x = rem - yl * p.Wo;
-          const int b = img0 + im, y = y0 + yl;
-          if (b < p.B && y < p.Ho) {
-            const size_t pix = (static_cast<size_t>(b) * p.Ho + y) * p.Wo + x;
-            if (p.gz_f32) {
-              if (c == 0) v.x = dpack_bf16(__ldg(p.gz_f32 + pix), 0.f);
-            } else if (p.co_off + c * 8 < p.cout) {
-              v = __ldg(reinterpret_cast<const uint4*>(p.gz + pix * p.cout + p.co_off) + c);
-            }
-          }
-        }
-        *reinterpret_cast<uint4*>(g_s + m * PPG + c * 16) = v;
+        if (c == 0 && b < p.B && y < p.Ho) v.x = dpack_bf16(__ldg(p.gz_f32 + (static_cast<size_t>(b) * p.Ho + y) * p.Wo + x), 0.f);
+        *reinterpret_cast<uint4*>(g_dst + m * PG + ((c ^ ((m >> SHG) & SWG)) << 4)) = v;
       }
     }
-    __syncthreads();
-    if (p.db && threadIdx.x < MT * 16) {
-      float s = 0.f;
-      for (int m = 0; m < M; ++m) s += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(g_s + m * PPG + threadIdx.x * 2));
-      dbacc += s;
+  };
+  __syncthreads();
+  for (int k = 0; k < p.nst - 1; ++k) {
+    const int t = blockIdx.x + k * gridDim.x;
+    if (t < p.n_tiles) load_tile(t, k);
+  }
+  int k = 0;
+  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++k) {
+    const int slot = k % p.nst;
+    __syncthreads();                                  // tile k-1 fully consumed: its stage takes tile k + nst - 1
+    {
+      const int t = tile + (p.nst - 1) * gridDim.x;
+      if (t < p.n_tiles) load_tile(t, (k + p.nst - 1) % p.nst);
+    }
+    mbar_wait(&bars[slot], (k / p.nst) & 1, 0x31);
+    const uint32_t a_u32 = dsmem_u32(ring + slot * stage_bytes);
+    const uint32_t g_u32 = a_u32 + p.a_bytes;
+    if (p.db) {                                       // bias gradient: every warp sums its share of the rows
+      constexpr int NCP = MT * 8;                     // 4-byte column pairs per row
+      const int cp = lane % NCP, ro = lane / NCP;
+      for (int m = warp * (32 / NCP) + ro; m < M; m += 9 * (32 / NCP)) {
+        uint32_t v;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v)
+                     : "r"(g_u32 + m * PG + (((cp >> 2) ^ ((m >> SHG) & SWG)) << 4) + (cp & 3) * 4));
+        db0 += dbf_lo(v); db1 += dbf_hi(v);
+      }
     }
     const int kA = (lane & 7) + ((lane >> 4) << 3);
     const int kB = (lane & 7) + (((lane >> 3) & 1) << 3);
@@ -335,15 +462,19 @@ dmma_wgrad_kernel(const DmmaWgradP p) {
       const int im = m / M_img;
       const int rem = m - im * M_img;
       const int yl = rem / p.Wo, x = rem - yl * p.Wo;
-      const uint32_t baddr = dsmem_u32(a_s) + ((im * TR + yl * S + ky) * TC + x * S + kx) * PPA + (lane >> 4) * 16;
-      const uint32_t aaddr = dsmem_u32(g_s) + (ch * 16 + kA) * PPG + ((lane >> 3) & 1) * 16;
+      const int n = (im * TR + yl * S + ky) * TC + x * S + kx;
+      const uint32_t brow = a_u32 + n * PA;
+      const int swb = (n >> SHA) & SWA;
+      const int r = ch * 16 + kA;
+      const uint32_t arow = g_u32 + r * PG;
+      const int swa = (r >> SHG) & SWG;
       uint32_t af[MT][4];
 #pragma unroll
-      for (int mt = 0; mt < MT; ++mt) ldsm_x4_t(aaddr + mt * 32, af[mt]);
+      for (int mt = 0; mt < MT; ++mt) ldsm_x4_t(arow + (((mt * 2 + ((lane >> 3) & 1)) ^ swa) << 4), af[mt]);
 #pragma unroll
       for (int np = 0; np < KS; ++np) {
         uint32_t b[4];
-        ldsm_x4_t(baddr + np * 32, b);
+        ldsm_x4_t(brow + (((np * 2 + (lane >> 4)) ^ swb) << 4), b);
 #pragma unroll
         for (int mt = 0; mt < MT; ++mt) {
           mma_bf16_16816(acc[mt][2 * np], af[mt], b[0], b[1]);
@@ -364,7 +495,19 @@ dmma_wgrad_kernel(const DmmaWgradP p) {
         const int ci = n * 8 + t2 + (i & 1);
         if (co < p.cout && ci < p.cin) atomicAdd(p.dw + (static_cast<size_t>(co) * p.cin + ci) * 9 + warp, acc[mt][n][i]);
       }
-  if (p.db && threadIdx.x < MT * 16 && p.co_off + threadIdx.x < p.cout) atomicAdd(p.db + p.co_off + threadIdx.x, dbacc);
+  if (p.db) {
+    constexpr int NCP = MT * 8;
+#pragma unroll
+    for (int o = NCP; o < 32; o <<= 1) {                // fold the row groups of the warp together
+      db0 += __shfl_xor_sync(0xffffffffu, db0, o);
+      db1 += __shfl_xor_sync(0xffffffffu, db1, o);
+    }
+    const int co = p.co_off + lane * 2;
+    if (lane < NCP && co < p.cout) {
+      atomicAdd(p.db + co, db0);
+      if (co + 1 < p.cout) atomicAdd(p.db + co + 1, db1);
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------- image end (Cin = 1)
@@ -523,7 +666,7 @@ static int pad16(int c) { return (c + 15) & ~15; }
 static int pad8(int c) { return (c + 7) & ~7; }
 
 static void dmma_tile_plan(int Hg, int Wg, int B, size_t bytes_per_src_pixel_row /*unused*/, int* TH, int* IMGS) {
-  const int target = 192;
+  const int target = 256;                              // 8 warps x one 32-pixel fragment pair
   if (Hg * Wg >= 128) {
     int th = (target + Wg - 1) / Wg;
     if (th > Hg) th = Hg;
@@ -536,30 +679,66 @@ static void dmma_tile_plan(int Hg, int Wg, int B, size_t bytes_per_src_pixel_row
     if (n < 1) n = 1;
     *TH = Hg; *IMGS = n;
   }
+  // small layers: enough tiles to put two on every SM matter more than full-size tiles
+  auto tiles = [&] { return ((Hg + *TH - 1) / *TH) * ((B + *IMGS - 1) / *IMGS); };
+  while (tiles() < 2 * sm_count() && (*IMGS) * (*TH) * Wg > 64) {
+    if (*IMGS > 1) *IMGS = (*IMGS + 1) / 2; else if (*TH > 1) *TH = (*TH + 1) / 2; else break;
+  }
 }
 
 template <int KS, int NT, int MODE>
 static int dmma_conv_launch_t(DmmaConvP& p, cudaStream_t st) {
-  constexpr int PP = KS * 32 + 16;
+  constexpr int PP = KS * 32 + 16, P = KS * 32;
   const int S = MODE == 0 ? p.stride : 1;
   const int Wg = MODE == 0 ? p.Wd : p.Wd / 2, Hg = MODE == 0 ? p.Hd : p.Hd / 2;
-  int TH, IMGS;
-  dmma_tile_plan(Hg, Wg, p.B, 0, &TH, &IMGS);
-  size_t smem;
-  for (;;) {
-    const int TR = MODE == 0 ? TH * S + 2 : TH + 1, TC = MODE == 0 ? Wg * S + 2 : Wg + 1;
-    smem = size_t(9) * NT * 8 * PP + size_t(IMGS) * TR * TC * PP;
-    if (smem <= 200 * 1024) break;
-    if (IMGS > 1) --IMGS; else if (TH > 1) TH = (TH + 1) / 2; else return set_error("dmma_conv: tile does not fit in shared memory");
+  // shared memory = weights + per-warp epilogue staging + barriers + a ring of source-tile buffers (1 KB aligned).
+  // First try to stay under 108 KB (two CTAs per SM) with at least 96 fragment rows per tile and two buffers; layers
+  // whose weights alone are too large for that (64 channels: 83 KB) run one CTA per SM with up to 200 KB.  Whatever
+  // room is left under the cap goes into more buffers (deeper prefetch), up to kDmmaMaxStages.
+  const size_t fixed = size_t(9) * NT * 8 * PP + (NT >= 2 ? size_t(kDmmaThreads / 32) * 32 * (NT * 16 + 16) : 0) +
+                       kDmmaMaxStages * 8 + 1024;
+  int TH = 0, IMGS = 0, TR = 0, TC = 0, nst = 2;
+  size_t smem = 0, tile_bytes = 0;
+  bool ok = false;
+  for (int attempt = 0; attempt < 2 && !ok; ++attempt) {
+    const size_t cap = attempt == 0 ? 108 * 1024 : 200 * 1024;
+    dmma_tile_plan(Hg, Wg, p.B, 0, &TH, &IMGS);
+    const int whole = Hg * Wg * (p.B < IMGS ? p.B : IMGS);
+    for (;;) {
+      TR = MODE == 0 ? TH * S + 2 : TH + 1; TC = MODE == 0 ? Wg * S + 2 : Wg + 1;
+      tile_bytes = (size_t(IMGS) * TR * TC * P + 1023) & ~size_t(1023);
+      smem = fixed + 2 * tile_bytes;
+      const int M = IMGS * TH * Wg;
+      if (attempt == 0 && M < 96 && M < whole) break;
+      if (smem <= cap && IMGS <= 256 && TR <= 256 && TC <= 256) {
+        ok = true;
+        // deeper ring only while it does not cost a resident CTA
+        auto ctas = [](size_t sm) { int c = int((224 * 1024) / (sm + 1024)); return c > 4 ? 4 : c; };
+        nst = 2;
+        while (nst < kDmmaMaxStages && fixed + (nst + 1) * tile_bytes <= cap &&
+               ctas(fixed + (nst + 1) * tile_bytes) == ctas(smem)) ++nst;
+        smem = fixed + nst * tile_bytes;
+        break;
+      }
+      if (IMGS > 1) --IMGS; else if (TH > 1) TH = (TH + 1) / 2; else break;
+    }
   }
-  p.TH = TH; p.IMGS = IMGS;
+  if (!ok) return set_error("dmma_conv: tile does not fit in shared memory");
+  p.TH = TH; p.IMGS = IMGS; p.nst = nst; p.tile_bytes = int(tile_bytes);
   p.tiles_y = (Hg + TH - 1) / TH;
   p.n_tiles = p.tiles_y * ((p.B + IMGS - 1) / IMGS);
+  CUtensorMap tmap;
+  memset(&tmap, 0, sizeof(tmap));
+  if (!p.in_f32) {
+    const uint64_t dims[4] = {uint64_t(p.cin), uint64_t(p.Ws), uint64_t(p.Hs), uint64_t(p.B)};
+    const uint32_t box[4] = {uint32_t(p.cin), uint32_t(TC), uint32_t(TR), uint32_t(IMGS)};
+    if (make_tmap_4d_bf16(&tmap, p.in, dims, box)) return 1;
+  }
   static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(dmma_conv_kernel<KS, NT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
-  int per_sm = int((220 * 1024) / (smem + 1024)); if (per_sm < 1) per_sm = 1; if (per_sm > 4) per_sm = 4;
+  if (!attr) { cudaFuncSetAttribute(dmma_conv_kernel<KS, NT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024); attr = true; }
+  int per_sm = int((224 * 1024) / (smem + 1024)); if (per_sm < 1) per_sm = 1; if (per_sm > 4) per_sm = 4;
   int grid = sm_count() * per_sm; if (grid > p.n_tiles) grid = p.n_tiles;
-  dmma_conv_kernel<KS, NT, MODE><<<grid, kDmmaThreads, smem, st>>>(p);
+  dmma_conv_kernel<KS, NT, MODE><<<grid, kDmmaThreads, smem, st>>>(p, tmap);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return set_cuda_error("dmma_conv launch", e);
   return 0;
@@ -579,25 +758,62 @@ static int dmma_conv_launch_n(DmmaConvP& p, cudaStream_t st) {
 
 template <int KS, int MT>
 static int dmma_wgrad_launch_t(DmmaWgradP& p, cudaStream_t st) {
-  constexpr int PPA = KS * 32 + 16, PPG = MT * 32 + 16;
-  int TH, IMGS;
-  dmma_tile_plan(p.Ho, p.Wo, p.B, 0, &TH, &IMGS);
-  size_t smem;
-  for (;;) {
-    const int TR = TH * p.stride + 2, TC = p.Wo * p.stride + 2;
-    const int M16 = (IMGS * TH * p.Wo + 15) & ~15;
-    smem = size_t(IMGS) * TR * TC * PPA + size_t(M16) * PPG;
-    if (smem <= 200 * 1024) break;
-    if (IMGS > 1) --IMGS; else if (TH > 1) TH = (TH + 1) / 2; else return set_error("dmma_wgrad: tile does not fit in shared memory");
+  constexpr int PA = KS * 32, PG = MT * 32;
+  const size_t fixed = kDwgMaxStages * 8 + 1024;
+  int TH = 0, IMGS = 0, TR = 0, TC = 0, nst = 2;
+  size_t a_bytes = 0, g_bytes = 0, smem = 0;
+  bool ok = false;
+  // two stages under 72 KB (three CTAs per SM) if the tile keeps >= 96 rows, else whatever fits in 200 KB
+  for (int attempt = 0; attempt < 2 && !ok; ++attempt) {
+    const size_t cap = attempt == 0 ? 72 * 1024 : 200 * 1024;
+    dmma_tile_plan(p.Ho, p.Wo, p.B, 0, &TH, &IMGS);
+    const int whole = p.Ho * p.Wo * (p.B < IMGS ? p.B : IMGS);
+    for (;;) {
+      TR = TH * p.stride + 2; TC = p.Wo * p.stride + 2;
+      const int M = IMGS * TH * p.Wo, M16 = (M + 15) & ~15;
+      a_bytes = (size_t(IMGS) * TR * TC * PA + 1023) & ~size_t(1023);
+      g_bytes = (size_t(M16) * PG + 1023) & ~size_t(1023);
+      smem = fixed + 2 * (a_bytes + g_bytes);
+      if (attempt == 0 && M < 96 && M < whole) break;
+      if (smem <= cap && IMGS <= 256 && TR <= 256 && TC <= 256 && TH <= 256) {
+        ok = true;
+        auto ctas = [](size_t sm) { int c = int((224 * 1024) / (sm + 1024)); return c > 3 ? 3 : c; };
+        nst = 2;
+        while (nst < kDwgMaxStages && fixed + (nst + 1) * (a_bytes + g_bytes) <= cap &&
+               ctas(fixed + (nst + 1) * (a_bytes + g_bytes)) == ctas(smem)) ++nst;
+        smem = fixed + nst * (a_bytes + g_bytes);
+        break;
+      }
+      if (IMGS > 1) --IMGS; else if (TH > 1) TH = (TH + 1) / 2; else break;
+    }
   }
-  p.TH = TH; p.IMGS = IMGS;
+  if (!ok) return set_error("dmma_wgrad: tile does not fit in shared memory");
+  p.TH = TH; p.IMGS = IMGS; p.nst = nst; p.a_bytes = int(a_bytes); p.g_bytes = int(g_bytes);
   p.tiles_y = (p.Ho + TH - 1) / TH;
   p.n_tiles = p.tiles_y * ((p.B + IMGS - 1) / IMGS);
+  CUtensorMap tmap_a, tmap_g;
+  memset(&tmap_g, 0, sizeof(tmap_g));
+  {
+    const uint64_t dims[4] = {uint64_t(p.cin), uint64_t(p.Wi), uint64_t(p.Hi), uint64_t(p.B)};
+    const uint32_t box[4] = {uint32_t(p.cin), uint32_t(TC), uint32_t(TR), uint32_t(IMGS)};
+    if (make_tmap_4d_bf16(&tmap_a, p.a, dims, box)) return 1;
+  }
+  if (!p.gz_f32) {
+    const uint64_t dims[4] = {uint64_t(p.cout), uint64_t(p.Wo), uint64_t(p.Ho), uint64_t(p.B)};
+    const uint32_t box[4] = {uint32_t(MT * 16), uint32_t(p.Wo), uint32_t(TH), uint32_t(IMGS)};
+    if (make_tmap_4d_bf16(&tmap_g, p.gz, dims, box)) return 1;
+  }
   static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(dmma_wgrad_kernel<KS, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
-  int per_sm = int((220 * 1024) / (smem + 1024)); if (per_sm < 1) per_sm = 1; if (per_sm > 3) per_sm = 3;
-  int grid = sm_count() * per_sm; if (grid > p.n_tiles) grid = p.n_tiles;
-  dmma_wgrad_kernel<KS, MT><<<grid, kDwgThreads, smem, st>>>(p);
+  if (!attr) { cudaFuncSetAttribute(dmma_wgrad_kernel<KS, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024); attr = true; }
+  int per_sm = int((224 * 1024) / (smem + 1024)); if (per_sm < 1) per_sm = 1; if (per_sm > 3) per_sm = 3;
+  // Every CTA ends with cout*cin*9 atomic adds, so a small layer wants few CTAs:  time(g) ~ tiles/g * t_tile +
+  // g * atomics / rate  is least at  g = sqrt(tiles * t_tile * rate / atomics)   (t_tile ~ 1.5 us, rate ~ 250 / ns).
+  const double atomics = double(MT * 16) * p.cin * 9;
+  int grid = int(sqrt(double(p.n_tiles) * 1500.0 * 250.0 / atomics));
+  if (grid < 16) grid = 16;
+  if (grid > sm_count() * per_sm) grid = sm_count() * per_sm;
+  if (grid > p.n_tiles) grid = p.n_tiles;
+  dmma_wgrad_kernel<KS, MT><<<grid, kDwgThreads, smem, st>>>(p, tmap_a, tmap_g);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return set_cuda_error("dmma_wgrad launch", e);
   return 0;

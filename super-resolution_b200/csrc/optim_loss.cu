@@ -161,6 +161,53 @@ __global__ void ragan_kernel(const float* __restrict__ u, const float* __restric
   if (threadIdx.x == 0) *loss = acc * scale;
 }
 
+// Same result with the batch reductions spread over the whole block: G = blockDim / n thread groups each sum a slice
+// of the batch per patch position (n <= blockDim; the prediction map of the patch discriminator has n = 25).
+__global__ void __launch_bounds__(1024)
+ragan_wide_kernel(const float* __restrict__ u, const float* __restrict__ v, int B, int n, float eps,
+                  float* __restrict__ loss, float* __restrict__ gu, float* __restrict__ gv) {
+  extern __shared__ float sm[];           // mu[n], mv[n], s1[n], s2[n], part[2][G][n]
+  const int G = blockDim.x / n;
+  float* mu = sm; float* mv = sm + n; float* s1 = sm + 2 * n; float* s2 = sm + 3 * n;
+  float* pa = sm + 4 * n; float* pc = pa + G * n;
+  const int g = threadIdx.x / n, j = threadIdx.x - g * n;
+  const bool act = g < G;
+  float a = 0.f, c = 0.f;
+  if (act) for (int b = g; b < B; b += G) { a += u[(size_t)b * n + j]; c += v[(size_t)b * n + j]; }
+  if (act) { pa[g * n + j] = a; pc[g * n + j] = c; }
+  __syncthreads();
+  if (threadIdx.x < n) {
+    float x = 0.f, y = 0.f;
+    for (int k = 0; k < G; ++k) { x += pa[k * n + threadIdx.x]; y += pc[k * n + threadIdx.x]; }
+    mu[threadIdx.x] = x / B; mv[threadIdx.x] = y / B;
+  }
+  __syncthreads();
+  a = 0.f; c = 0.f;
+  if (act) for (int b = g; b < B; b += G) {
+    a += sigmoidf(-(eps + u[(size_t)b * n + j] - mv[j]));
+    c += sigmoidf(eps + v[(size_t)b * n + j] - mu[j]);
+  }
+  if (act) { pa[g * n + j] = a; pc[g * n + j] = c; }
+  __syncthreads();
+  if (threadIdx.x < n) {
+    float x = 0.f, y = 0.f;
+    for (int k = 0; k < G; ++k) { x += pa[k * n + threadIdx.x]; y += pc[k * n + threadIdx.x]; }
+    s1[threadIdx.x] = x; s2[threadIdx.x] = y;
+  }
+  __syncthreads();
+  const float scale = 0.5f / (float(B) * n);
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < B * n; i += blockDim.x) {
+    const int jj = i % n;
+    const float x1 = eps + u[i] - mv[jj], x2 = eps + v[i] - mu[jj];
+    acc += softplus(-x1) + softplus(x2);
+    if (gu) gu[i] = scale * (-sigmoidf(-x1) - s2[jj] / B);
+    if (gv) gv[i] = scale * (sigmoidf(x2) + s1[jj] / B);
+  }
+  acc = block_sum(acc);
+  if (threadIdx.x == 0) *loss = acc * scale;
+}
+
 // ------------------------------------------------------------------ gradient penalty
 __global__ void gp_fwd_kernel(const float* __restrict__ g, int B, int n, float coef, float* __restrict__ norms,
                               float* __restrict__ loss) {
@@ -234,7 +281,12 @@ extern "C" int srb_pixel_losses(const float* gen, const float* gt, const float* 
 
 extern "C" int srb_ragan(const float* u, const float* v, int B, int n, float eps, float* loss, float* gu, float* gv,
                          void* stream) {
-  ragan_kernel<<<1, 256, 4 * n * sizeof(float), (cudaStream_t)stream>>>(u, v, B, n, eps, loss, gu, gv);
+  if (n <= 512) {
+    const int G = 1024 / n;
+    ragan_wide_kernel<<<1, 1024, (4 * n + 2 * G * n) * sizeof(float), (cudaStream_t)stream>>>(u, v, B, n, eps, loss, gu, gv);
+  } else {
+    ragan_kernel<<<1, 256, 4 * n * sizeof(float), (cudaStream_t)stream>>>(u, v, B, n, eps, loss, gu, gv);
+  }
   SRB_CHK("ragan");
   return 0;
 }
