@@ -62,6 +62,7 @@ struct DmmaConvP {
   int stride;                  // MODE 0
   int TH, IMGS;                // tile = IMGS images x TH rows (MODE 0: destination rows; MODE 1: phase-grid rows)
   int nst, tile_bytes;         // ring of nst source-tile buffers, tile_bytes apart (multiple of 1024)
+  uint32_t mg_img, mg_w;       // ceil(2^32 / (TH*Wg)), ceil(2^32 / Wg): exact division of fragment-row indices (< 2^16)
   int tiles_y, n_tiles;
   int act;                     // 0 none, 1 LeakyReLU(slope), 2 multiply by (ref > 0 ? 1 : slope)
   float slope;
@@ -143,6 +144,13 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
       }
     }
   };
+  float bia[NT][2];                                   // this lane's accumulator columns: n*8 + 2*(lane&3), +1
+#pragma unroll
+  for (int n = 0; n < NT; ++n) {
+    const int col = n * 8 + (lane & 3) * 2;
+    bia[n][0] = (NT >= 2 && p.bias) ? __ldg(p.bias + col) : 0.f;
+    bia[n][1] = (NT >= 2 && p.bias) ? __ldg(p.bias + col + 1) : 0.f;
+  }
   __syncthreads();                                    // barriers initialised (weights: covered by the loop's barrier)
   for (int k = 0; k < p.nst - 1; ++k) {
     const int t = blockIdx.x + k * gridDim.x;
@@ -166,22 +174,22 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
       const int ph = MODE == 0 ? 0 : it / npair;
       const int pr = MODE == 0 ? it : it - ph * npair;
       const int py = ph >> 1, px = ph & 1;
-      float acc[2][NT][4];
+      float acc[2][NT][4];                            // NT >= 2: starts from the bias (the epilogue adds nothing)
 #pragma unroll
       for (int f = 0; f < 2; ++f)
 #pragma unroll
         for (int n = 0; n < NT; ++n)
 #pragma unroll
-          for (int i = 0; i < 4; ++i) acc[f][n][i] = 0.f;
+          for (int i = 0; i < 4; ++i) acc[f][n][i] = NT >= 2 ? bia[n][i & 1] : 0.f;
       // per-lane tile pixel (at tap 0,0) of the fragment row this lane addresses, for the two fragments
       int nbase[2];
 #pragma unroll
       for (int f = 0; f < 2; ++f) {
         int m = (pr * 2 + f) * 16 + (lane & 15);
         if (m >= M) m = 0;
-        const int im = m / M_img;
+        const int im = __umulhi(m, p.mg_img);
         const int rem = m - im * M_img;
-        const int yl = rem / Wg, x = rem - yl * Wg;
+        const int yl = __umulhi(rem, p.mg_w), x = rem - yl * Wg;
         nbase[f] = (im * TR + yl * S) * TC + x * S;
       }
       const int hi = lane >> 4;
@@ -234,51 +242,57 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
         // 16-byte chunks: consecutive lanes cover consecutive channels of consecutive pixels (coalesced stores and,
         // for the mask epilogue, coalesced reads of the reference activation).
         constexpr int SP = NT * 16 + 16;
-        uint8_t* stg = stage_s + warp * (32 * SP);
+        constexpr int RPI = 32 / NT;                  // staging rows covered by the warp per 16-byte pass
+        const uint32_t stg = dsmem_u32(stage_s) + warp * (32 * SP);
         // destination pixel of staging row `lane` (-1: nothing to store)
-        long long mypix = -1;
+        int mypix = -1;
         {
           const int m = pr * 32 + lane;
           if (m < M && (lane < 16 || two)) {
-            const int im = m / M_img;
+            const int im = __umulhi(m, p.mg_img);
             const int rem = m - im * M_img;
-            const int yl = rem / Wg, x = rem - yl * Wg;
+            const int yl = __umulhi(rem, p.mg_w), x = rem - yl * Wg;
             const int b = img0 + im, yg = y0 + yl;
             if (b < p.B && yg < Hg) {
               const int yd = MODE == 0 ? yg : 2 * yg + py;
               const int xd = MODE == 0 ? x : 2 * x + px;
-              mypix = (static_cast<long long>(b) * p.Hd + yd) * p.Wd + xd;
+              mypix = (b * p.Hd + yd) * p.Wd + xd;
             }
           }
         }
+        if (p.act == 1) {                             // LeakyReLU, slope in (0, 1): max(v, slope * v)
 #pragma unroll
-        for (int f = 0; f < 2; ++f) {
+          for (int f = 0; f < 2; ++f)
 #pragma unroll
-          for (int hrow = 0; hrow < 2; ++hrow) {
-            const int r = f * 16 + g + hrow * 8;
+            for (int n = 0; n < NT; ++n)
 #pragma unroll
-            for (int n = 0; n < NT; ++n) {
-              const int col = n * 8 + t2;
-              float v0 = acc[f][n][hrow * 2], v1 = acc[f][n][hrow * 2 + 1];
-              if (p.bias) { v0 += __ldg(p.bias + col); v1 += __ldg(p.bias + col + 1); }
-              if (p.act == 1) {
-                v0 = v0 > 0.f ? v0 : v0 * p.slope;
-                v1 = v1 > 0.f ? v1 : v1 * p.slope;
-              }
-              *reinterpret_cast<uint32_t*>(stg + r * SP + col * 2) = dpack_bf16(v0, v1);
-            }
-          }
+              for (int i = 0; i < 4; ++i) acc[f][n][i] = fmaxf(acc[f][n][i], acc[f][n][i] * p.slope);
+        }
+        {
+          const uint32_t mine = stg + g * SP + t2 * 2;
+#pragma unroll
+          for (int f = 0; f < 2; ++f)
+#pragma unroll
+            for (int hrow = 0; hrow < 2; ++hrow)
+#pragma unroll
+              for (int n = 0; n < NT; ++n)
+                asm volatile("st.shared.b32 [%0], %1;" ::"r"(mine + (f * 16 + hrow * 8) * SP + n * 16),
+                             "r"(dpack_bf16(acc[f][n][hrow * 2], acc[f][n][hrow * 2 + 1])) : "memory");
         }
         __syncwarp();
+        const int part = lane % NT, r0 = lane / NT;
+        const bool masked = p.act == 2;
 #pragma unroll
         for (int i = 0; i < NT; ++i) {
-          const int c = lane + 32 * i;
-          const int r = c / NT, part = c - r * NT;
-          const long long pix = __shfl_sync(0xffffffffu, mypix, r);
+          const int r = r0 + i * RPI;
+          const int pix = __shfl_sync(0xffffffffu, mypix, r);
           if (pix < 0) continue;
-          uint4 v = *reinterpret_cast<const uint4*>(stg + r * SP + part * 16);
-          if (p.act == 2) {
-            const uint4 m4 = __ldg(reinterpret_cast<const uint4*>(p.ref + pix * p.cout) + part);
+          uint4 v;
+          asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                       : "r"(stg + r * SP + part * 16));
+          const size_t off = static_cast<size_t>(static_cast<uint32_t>(pix) * static_cast<uint32_t>(NT)) + part;   // in 16-byte units
+          if (masked) {
+            const uint4 m4 = __ldg(reinterpret_cast<const uint4*>(p.ref) + off);
             const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
             uint32_t vw[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -287,7 +301,7 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
                                  dbf_hi(vw[q]) * (dbf_hi(mw[q]) > 0.f ? 1.f : p.slope));
             v = make_uint4(vw[0], vw[1], vw[2], vw[3]);
           }
-          *(reinterpret_cast<uint4*>(p.out + pix * p.cout) + part) = v;
+          *(reinterpret_cast<uint4*>(p.out) + off) = v;
         }
         __syncwarp();
       } else {
@@ -666,15 +680,16 @@ static int pad16(int c) { return (c + 15) & ~15; }
 static int pad8(int c) { return (c + 7) & ~7; }
 
 static void dmma_tile_plan(int Hg, int Wg, int B, size_t bytes_per_src_pixel_row /*unused*/, int* TH, int* IMGS) {
-  const int target = 256;                              // 8 warps x one 32-pixel fragment pair
+  const int target = 256;                              // at most 8 warps x one 32-pixel fragment pair
   if (Hg * Wg >= 128) {
-    int th = (target + Wg - 1) / Wg;
+    int th = target / Wg;
+    if (th < 1) th = 1;
     if (th > Hg) th = Hg;
     const int nt = (Hg + th - 1) / th;
     th = (Hg + nt - 1) / nt;
     *TH = th; *IMGS = 1;
   } else {
-    int n = (target + Hg * Wg - 1) / (Hg * Wg);
+    int n = target / (Hg * Wg);
     if (n > B) n = B;
     if (n < 1) n = 1;
     *TH = Hg; *IMGS = n;
@@ -725,6 +740,9 @@ static int dmma_conv_launch_t(DmmaConvP& p, cudaStream_t st) {
   }
   if (!ok) return set_error("dmma_conv: tile does not fit in shared memory");
   p.TH = TH; p.IMGS = IMGS; p.nst = nst; p.tile_bytes = int(tile_bytes);
+  if (Wg < 2) return set_error("dmma_conv: map too narrow");
+  p.mg_img = uint32_t(((1ull << 32) + uint64_t(TH * Wg) - 1) / uint64_t(TH * Wg));
+  p.mg_w = uint32_t(((1ull << 32) + uint64_t(Wg) - 1) / uint64_t(Wg));
   p.tiles_y = (Hg + TH - 1) / TH;
   p.n_tiles = p.tiles_y * ((p.B + IMGS - 1) / IMGS);
   CUtensorMap tmap;
