@@ -98,6 +98,27 @@ int make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4]
   return 0;
 }
 
+int make_tmap_3d_f32(CUtensorMap* out, const void* base, uint64_t W, uint64_t H, uint64_t B, uint32_t box_w,
+                     uint32_t box_h) {
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) return set_error("cuTensorMapEncodeTiled entry point not available");
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || ((W * 4) & 15) || ((uint64_t(box_w) * 4) & 15) || box_w > 256 || box_h > 256)
+    return set_error("tensor map (3d f32): base, row pitch and box row must be multiples of 16 bytes, box <= 256");
+  cuuint64_t d[3] = {W, H, B};
+  cuuint64_t strides[2] = {W * 4, W * H * 4};
+  cuuint32_t b[3] = {box_w, box_h, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(base), d, strides, b, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[128];
+    snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled (3d f32) failed with CUresult %d", int(r));
+    return set_error(buf);
+  }
+  return 0;
+}
+
 const char* last_error();
 
 }  // namespace srb

@@ -21,6 +21,10 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64
 // 4-D tiled map over a dense bf16 [d3][d2][d1][d0] tensor (d0 innermost; the box takes 16/32/64 of its elements);
 // swizzle = the innermost box extent in bytes (32B/64B/128B), out-of-bounds elements read as zero.
 int make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint32_t box[4]);
+// 3-D tiled map over a dense fp32 [B][H][W] image stack, box = box_h rows x box_w columns of one image, no swizzle,
+// out-of-bounds elements (halo) read as zero.
+int make_tmap_3d_f32(CUtensorMap* out, const void* base, uint64_t W, uint64_t H, uint64_t B, uint32_t box_w,
+                     uint32_t box_h);
 
 inline int ceil_div(long long a, long long b) { return int((a + b - 1) / b); }
 

@@ -15,6 +15,7 @@
 //   dmma_wgrad_kernel<KS,MT>       dW[co][ci][t] += sum_pixels gz[p][co] * a[p*s + t][ci];  db[co] += sum gz
 //   dl1_* kernels                  the 1-channel image end of the stack (Cin = 1) on CUDA cores in fp32
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -649,6 +650,105 @@ dl1_wgrad_kernel(const __nv_bfloat16* __restrict__ gz, const float* __restrict__
   else if (db) atomicAdd(db + c, acc);
 }
 
+// Tensor-core form of the same sums for C == 16 and W % 16 == 0:  D[c][n] = sum_p gz[p][c] * Bm[p][n]  with
+// Bm[p][0..8] = img[p + tap n], Bm[p][9] = 1 (the bias gradient), as m16n8k16 MMAs over 16-pixel chunks of an image row
+// (two n8 tiles: taps 0-7 | tap 8, ones).  The fp32 image is split into bf16 hi + lo parts (two MMAs), which keeps
+// the products exact to 2^-17; gz is bf16 already.  Tiles (one image band: gz rows by 4-D TMA, the image rows with
+// their halo by 3-D TMA from column x = -4, zero-filled at the borders) go through a ring of p.nst stages; each warp takes every 8th chunk.
+struct Dl1WgradP {
+  float* dw; float* db;
+  int B, H, W, TH, bands, n_tiles, nst, g_bytes, stage_bytes, TCp;
+};
+
+__global__ void __launch_bounds__(256)
+dl1_wgrad_tc_kernel(const Dl1WgradP p, const __grid_constant__ CUtensorMap tmap_g,
+                    const __grid_constant__ CUtensorMap tmap_img) {
+  extern __shared__ __align__(1024) uint8_t dsm[];
+  uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dsm) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + p.nst * p.stage_bytes);
+  float* red = reinterpret_cast<float*>(bars + 8);                    // [16][10]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const int TR = p.TH + 2;
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmap_g);
+    tma_prefetch_desc(&tmap_img);
+    for (int i = 0; i < p.nst; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+  }
+  if (threadIdx.x < 160) red[threadIdx.x] = 0.f;
+  auto load_tile = [&](int tile, int slot) {
+    if (threadIdx.x != 0) return;
+    const int b = tile / p.bands, y0 = (tile - b * p.bands) * p.TH;
+    uint8_t* dst = ring + slot * p.stage_bytes;
+    mbar_expect_tx(&bars[slot], static_cast<uint32_t>(p.TH * p.W * 32 + TR * p.TCp * 4));
+    tma_load_4d(dst, &tmap_g, 0, 0, y0, b, &bars[slot]);
+    tma_load_3d(dst + p.g_bytes, &tmap_img, -4, y0 - 1, b, &bars[slot]);   // shared-memory column j holds x = j - 4
+  };
+  __syncthreads();
+  for (int k = 0; k < p.nst - 1; ++k) {
+    const int tt = blockIdx.x + k * gridDim.x;
+    if (tt < p.n_tiles) load_tile(tt, k);
+  }
+  float acc1[4] = {0.f, 0.f, 0.f, 0.f}, acc2[4] = {0.f, 0.f, 0.f, 0.f};
+  // image-tile word offset of this lane's B rows: tap g for the first n-tile, tap 8 (lanes with g == 0) for the second
+  const int off1 = (g / 3) * p.TCp + (g % 3) + 3 + 2 * t;
+  const int off2 = 2 * p.TCp + 2 + 3 + 2 * t;
+  const int kA = (lane & 7) + ((lane >> 4) << 3);
+  const int chunks_x = p.W >> 4;
+  int k = 0;
+  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x, ++k) {
+    const int slot = k % p.nst;
+    __syncthreads();
+    {
+      const int tt = tile + (p.nst - 1) * gridDim.x;
+      if (tt < p.n_tiles) load_tile(tt, (k + p.nst - 1) % p.nst);
+    }
+    mbar_wait(&bars[slot], (k / p.nst) & 1, 0x32);
+    const uint32_t g_u32 = dsmem_u32(ring + slot * p.stage_bytes);
+    const float* im = reinterpret_cast<const float*>(ring + slot * p.stage_bytes + p.g_bytes);
+    for (int ch = warp; ch < p.TH * chunks_x; ch += 8) {
+      const int r = ch / chunks_x, x0 = (ch - r * chunks_x) << 4;
+      uint32_t af[4];
+      {
+        const int n = ch * 16 + kA;
+        ldsm_x4_t(g_u32 + n * 32 + ((((lane >> 3) & 1) ^ ((n >> 2) & 1)) << 4), af);
+      }
+      const float* row = im + r * p.TCp + x0;
+      float v[4] = {row[off1], row[off1 + 1], row[off1 + 8], row[off1 + 9]};
+      uint32_t hi0 = dpack_bf16(v[0], v[1]), hi1 = dpack_bf16(v[2], v[3]);
+      uint32_t lo0 = dpack_bf16(v[0] - dbf_lo(hi0), v[1] - dbf_hi(hi0));
+      uint32_t lo1 = dpack_bf16(v[2] - dbf_lo(hi1), v[3] - dbf_hi(hi1));
+      mma_bf16_16816(acc1, af, hi0, hi1);
+      mma_bf16_16816(acc1, af, lo0, lo1);
+      if (g == 0) {
+        v[0] = row[off2]; v[1] = row[off2 + 1]; v[2] = row[off2 + 8]; v[3] = row[off2 + 9];
+        hi0 = dpack_bf16(v[0], v[1]); hi1 = dpack_bf16(v[2], v[3]);
+        lo0 = dpack_bf16(v[0] - dbf_lo(hi0), v[1] - dbf_hi(hi0));
+        lo1 = dpack_bf16(v[2] - dbf_lo(hi1), v[3] - dbf_hi(hi1));
+      } else {
+        hi0 = hi1 = g == 1 ? 0x3f803f80u : 0u;          // bf16 1.0 pairs: column 9 sums gz (bias gradient)
+        lo0 = lo1 = 0u;
+      }
+      mma_bf16_16816(acc2, af, hi0, hi1);
+      mma_bf16_16816(acc2, af, lo0, lo1);
+    }
+  }
+  // accumulator (row g | g+8, columns 2t, 2t+1) -> red[c][n];  second tile: column 0 = tap 8, column 1 = bias
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = g + (i >> 1) * 8, n = 2 * t + (i & 1);
+    atomicAdd(&red[c * 10 + n], acc1[i]);
+    if (t == 0) atomicAdd(&red[c * 10 + 8 + (i & 1)], acc2[i]);
+  }
+  __syncthreads();
+  if (threadIdx.x < 160) {
+    const int c = threadIdx.x / 10, n = threadIdx.x - c * 10;
+    if (n < 9) atomicAdd(p.dw + c * 9 + n, red[threadIdx.x]);
+    else if (p.db) atomicAdd(p.db + c, red[threadIdx.x]);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- weight packs
 // One launch packs every layer of a discriminator: fp32 OIHW (flat parameter buffer) -> bf16 [9][rows][kpad].
 //   kind 0 (forward, and MODE 1 input gradient of stride-2 layers uses kind 2):  wp[t][co][ci] = w[co][ci][t]
@@ -930,6 +1030,32 @@ extern "C" int srb_dl1_dgrad(const void* gz_bf16, const float* w, float* gx, int
 extern "C" int srb_dl1_wgrad(const void* gz_bf16, const float* img, float* dw, float* db, int C, int B, int H, int W,
                              void* stream) {
   if (!gz_bf16 || !img || !dw) return set_error("dl1_wgrad: null pointer");
+  if (C == 16 && W % 16 == 0 && W + 8 <= 256) {          // tensor-core kernel
+    Dl1WgradP p{};
+    p.dw = dw; p.db = db; p.B = B; p.H = H; p.W = W;
+    p.TH = H < 8 ? H : 8;
+    p.bands = (H + p.TH - 1) / p.TH;
+    p.n_tiles = B * p.bands;
+    p.TCp = W + 8;                                       // columns x = -4 .. W+3: TMA box starts must be 16-byte aligned
+    p.g_bytes = (p.TH * W * 32 + 1023) & ~1023;
+    p.stage_bytes = p.g_bytes + (((p.TH + 2) * p.TCp * 4 + 1023) & ~1023);
+    p.nst = 3;
+    const size_t smem = 1024 + size_t(p.nst) * p.stage_bytes + 64 + 160 * 4;
+    CUtensorMap tg, ti;
+    const uint64_t dims[4] = {16, uint64_t(W), uint64_t(H), uint64_t(B)};
+    const uint32_t box[4] = {16, uint32_t(W), uint32_t(p.TH), 1};
+    if (make_tmap_4d_bf16(&tg, gz_bf16, dims, box)) return 1;
+    if (make_tmap_3d_f32(&ti, img, W, H, B, p.TCp, p.TH + 2)) return 1;
+    static bool attr = false;
+    if (!attr) { cudaFuncSetAttribute(dl1_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; }
+    if (smem > 100 * 1024) return set_error("dl1_wgrad: band does not fit in shared memory");
+    int per_sm = int((224 * 1024) / (smem + 1024)); if (per_sm < 1) per_sm = 1; if (per_sm > 4) per_sm = 4;
+    int grid = sm_count() * per_sm; if (grid > p.n_tiles) grid = p.n_tiles;
+    dl1_wgrad_tc_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(p, tg, ti);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_cuda_error("dl1_wgrad launch", e);
+    return 0;
+  }
   int TH = 8; if (TH > H) TH = H;
   while (TH > 1 && size_t(TH + 2) * (W + 2) * 4 + 16 + size_t(TH) * W * C * 2 > 96 * 1024) TH = (TH + 1) / 2;
   const size_t smem = size_t(TH + 2) * (W + 2) * 4 + 16 + size_t(TH) * W * C * 2;

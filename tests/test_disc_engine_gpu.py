@@ -131,12 +131,16 @@ def test_dmma_conv_forward_dgrad_wgrad(case):
     assert (db - 0.25 - br.grad).abs().max().item() <= 2e-3 * br.grad.abs().max().item() + 1e-4
 
 
-@pytest.mark.parametrize("C1", [16, 32])
-def test_image_end_kernels(C1):
+# (3, 20, 32) and (2, 80, 80) with 16 channels take the tensor-core weight-gradient kernel (W % 16 == 0), the first
+# with a partial last band; the other cases take the CUDA-core kernel
+@pytest.mark.parametrize("C1,shape", [(16, (5, 18, 22)), (32, (5, 18, 22)), (16, (3, 20, 32)), (16, (2, 80, 80)),
+                                      (32, (2, 16, 16))])
+def test_image_end_kernels(C1, shape):
     dev = _dev()
     from srb200 import _lib as L
     lib = L.lib()
-    B, H, W = 5, 18, 22
+    torch.backends.cudnn.allow_tf32 = False          # the torch reference must be true fp32 (cuDNN picks TF32 at 80x80)
+    B, H, W = shape
     g = torch.Generator().manual_seed(C1)
     img = torch.randn(B, 1, H, W, generator=g).to(dev)
     w = (torch.randn(C1, 1, 3, 3, generator=g) / 3).to(dev)
