@@ -48,4 +48,12 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 #endif
 
+// csrc/disc_mma.cu: warp-MMA 3x3 convolution / weight gradient with explicit memory pitches (see there)
+int dmma_conv_pitched(const void* in_bf16, const float* in_f32, int cin, const void* w_packed, const float* bias,
+                      int cout, void* out_bf16, float* out_f32, const void* ref, int B, int Hs, int Ws, int Hd,
+                      int Wd, int Hsp, int Wsp, int Hdp, int Wdp, int stride, int transposed, int act, float slope,
+                      void* stream);
+int dmma_wgrad_pitched(const void* gz_bf16, const float* gz_f32, int cout, const void* a_bf16, int cin, float* dw,
+                       float* db, int B, int Hi, int Wi, int Hip, int Wip, int Ho, int Wo, int stride, void* stream);
+
 }  // namespace srb

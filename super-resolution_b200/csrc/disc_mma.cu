@@ -59,6 +59,7 @@ struct DmmaConvP {
   float* out_f32;              // fp32 [B][Hd][Wd] (cout == 1) or null
   const __nv_bfloat16* ref;    // act == 2: mask reference, geometry of out
   int B, Hs, Ws, Hd, Wd;       // source / destination maps
+  int Hsp, Wsp, Hdp, Wdp;      // their pitches in memory (rows, pixels per row); PNHWC buffers carry one zero row/column
   int cin, cout;               // real channel counts (<= KS*16, <= NT*8)
   int stride;                  // MODE 0
   int TH, IMGS;                // tile = IMGS images x TH rows (MODE 0: destination rows; MODE 1: phase-grid rows)
@@ -257,7 +258,7 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
             if (b < p.B && yg < Hg) {
               const int yd = MODE == 0 ? yg : 2 * yg + py;
               const int xd = MODE == 0 ? x : 2 * x + px;
-              mypix = (b * p.Hd + yd) * p.Wd + xd;
+              mypix = (b * p.Hdp + yd) * p.Wdp + xd;
             }
           }
         }
@@ -321,7 +322,7 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
           if (b >= p.B || yg >= Hg) continue;
           const int yd = MODE == 0 ? yg : 2 * yg + py;
           const int xd = MODE == 0 ? x : 2 * x + px;
-          const size_t pix = (static_cast<size_t>(b) * p.Hd + yd) * p.Wd + xd;
+          const size_t pix = (static_cast<size_t>(b) * p.Hdp + yd) * p.Wdp + xd;
 #pragma unroll
           for (int n = 0; n < NT; ++n) {
             const int col = n * 8 + t2;
@@ -367,6 +368,7 @@ struct DmmaWgradP {
   int B, Hi, Wi, Ho, Wo, cin, cout, stride;
   int co_off;                  // first output channel handled by this launch (MT*16 channels from there)
   int TH, IMGS, tiles_y, n_tiles;
+  int Hip, Wip;                // pitches of a in memory (rows, pixels per row)
   int nst, a_bytes, g_bytes;   // ring of nst stages; activation / gradient tile sizes (multiples of 1024)
 };
 
@@ -848,7 +850,7 @@ static int dmma_conv_launch_t(DmmaConvP& p, cudaStream_t st) {
   CUtensorMap tmap;
   memset(&tmap, 0, sizeof(tmap));
   if (!p.in_f32) {
-    const uint64_t dims[4] = {uint64_t(p.cin), uint64_t(p.Ws), uint64_t(p.Hs), uint64_t(p.B)};
+    const uint64_t dims[4] = {uint64_t(p.cin), uint64_t(p.Wsp), uint64_t(p.Hsp), uint64_t(p.B)};
     const uint32_t box[4] = {uint32_t(p.cin), uint32_t(TC), uint32_t(TR), uint32_t(IMGS)};
     if (make_tmap_4d_bf16(&tmap, p.in, dims, box)) return 1;
   }
@@ -912,7 +914,7 @@ static int dmma_wgrad_launch_t(DmmaWgradP& p, cudaStream_t st) {
   CUtensorMap tmap_a, tmap_g;
   memset(&tmap_g, 0, sizeof(tmap_g));
   {
-    const uint64_t dims[4] = {uint64_t(p.cin), uint64_t(p.Wi), uint64_t(p.Hi), uint64_t(p.B)};
+    const uint64_t dims[4] = {uint64_t(p.cin), uint64_t(p.Wip), uint64_t(p.Hip), uint64_t(p.B)};
     const uint32_t box[4] = {uint32_t(p.cin), uint32_t(TC), uint32_t(TR), uint32_t(IMGS)};
     if (make_tmap_4d_bf16(&tmap_a, p.a, dims, box)) return 1;
   }
@@ -941,9 +943,14 @@ static int dmma_wgrad_launch_t(DmmaWgradP& p, cudaStream_t st) {
 
 using namespace srb;
 
-extern "C" int srb_dmma_conv(const void* in_bf16, const float* in_f32, int cin, const void* w_packed, const float* bias,
-                             int cout, void* out_bf16, float* out_f32, const void* ref, int B, int Hs, int Ws, int Hd,
-                             int Wd, int stride, int transposed, int act, float slope, void* stream) {
+namespace srb {
+// The C entry point with explicit memory pitches for the source (Hsp rows x Wsp pixels per image) and for the
+// destination / mask reference (Hdp x Wdp): lets the generator's PNHWC buffers (one zero row and column per image)
+// be read and written in place.  Used by csrc/gen_edge.cu for conv3.2.
+int dmma_conv_pitched(const void* in_bf16, const float* in_f32, int cin, const void* w_packed, const float* bias,
+                      int cout, void* out_bf16, float* out_f32, const void* ref, int B, int Hs, int Ws, int Hd,
+                      int Wd, int Hsp, int Wsp, int Hdp, int Wdp, int stride, int transposed, int act, float slope,
+                      void* stream) {
   if ((!in_bf16 && !in_f32) || !w_packed || (!out_bf16 && !out_f32)) return set_error("dmma_conv: null pointer");
   if (in_f32 && cin != 1) return set_error("dmma_conv: fp32 source must be single-channel");
   if (!in_f32 && cin != 16 && cin != 32 && cin != 64) return set_error("dmma_conv: input channels must be 16, 32 or 64");
@@ -957,6 +964,9 @@ extern "C" int srb_dmma_conv(const void* in_bf16, const float* in_f32, int cin, 
   p.in = (const __nv_bfloat16*)in_bf16; p.in_f32 = in_f32; p.w = (const __nv_bfloat16*)w_packed; p.bias = bias;
   p.out = (__nv_bfloat16*)out_bf16; p.out_f32 = out_f32; p.ref = (const __nv_bfloat16*)ref;
   p.B = B; p.Hs = Hs; p.Ws = Ws; p.Hd = Hd; p.Wd = Wd; p.cin = cin; p.cout = cout; p.stride = stride;
+  p.Hsp = Hsp; p.Wsp = Wsp; p.Hdp = Hdp; p.Wdp = Wdp;
+  if (Hsp < Hs || Wsp < Ws || Hdp < Hd || Wdp < Wd) return set_error("dmma_conv: pitch smaller than the map");
+  if (in_f32 && (Hsp != Hs || Wsp != Ws)) return set_error("dmma_conv: fp32 source must be dense");
   p.act = act; p.slope = slope;
   cudaStream_t st = (cudaStream_t)stream;
   const int ks = pad16(cin) / 16;
@@ -976,8 +986,8 @@ extern "C" int srb_dmma_conv(const void* in_bf16, const float* in_f32, int cin, 
   return set_error("dmma_conv: unsupported channel count");
 }
 
-extern "C" int srb_dmma_wgrad(const void* gz_bf16, const float* gz_f32, int cout, const void* a_bf16, int cin, float* dw,
-                              float* db, int B, int Hi, int Wi, int Ho, int Wo, int stride, void* stream) {
+int dmma_wgrad_pitched(const void* gz_bf16, const float* gz_f32, int cout, const void* a_bf16, int cin, float* dw,
+                       float* db, int B, int Hi, int Wi, int Hip, int Wip, int Ho, int Wo, int stride, void* stream) {
   if ((!gz_bf16 && !gz_f32) || !a_bf16 || !dw) return set_error("dmma_wgrad: null pointer");
   if (gz_f32 && cout != 1) return set_error("dmma_wgrad: fp32 gradient must be single-channel");
   if (cin != 16 && cin != 32 && cin != 64) return set_error("dmma_wgrad: input channels must be 16, 32 or 64");
@@ -986,6 +996,8 @@ extern "C" int srb_dmma_wgrad(const void* gz_bf16, const float* gz_f32, int cout
   DmmaWgradP p{};
   p.gz = (const __nv_bfloat16*)gz_bf16; p.gz_f32 = gz_f32; p.a = (const __nv_bfloat16*)a_bf16; p.dw = dw; p.db = db;
   p.B = B; p.Hi = Hi; p.Wi = Wi; p.Ho = Ho; p.Wo = Wo; p.cin = cin; p.cout = cout; p.stride = stride;
+  p.Hip = Hip; p.Wip = Wip;
+  if (Hip < Hi || Wip < Wi) return set_error("dmma_wgrad: pitch smaller than the map");
   cudaStream_t st = (cudaStream_t)stream;
   const int ks = cin / 16, mt = pad16(cout) / 16;
 #define SRB_WG(K, M) if (ks == K && mt == M) return dmma_wgrad_launch_t<K, M>(p, st);
@@ -997,6 +1009,19 @@ extern "C" int srb_dmma_wgrad(const void* gz_bf16, const float* gz_f32, int cout
     return dmma_wgrad_launch_t<4, 2>(p, st);
   }
   return set_error("dmma_wgrad: unsupported channel count");
+}
+}  // namespace srb
+
+extern "C" int srb_dmma_conv(const void* in_bf16, const float* in_f32, int cin, const void* w_packed, const float* bias,
+                             int cout, void* out_bf16, float* out_f32, const void* ref, int B, int Hs, int Ws, int Hd,
+                             int Wd, int stride, int transposed, int act, float slope, void* stream) {
+  return dmma_conv_pitched(in_bf16, in_f32, cin, w_packed, bias, cout, out_bf16, out_f32, ref, B, Hs, Ws, Hd, Wd, Hs, Ws,
+                           Hd, Wd, stride, transposed, act, slope, stream);
+}
+
+extern "C" int srb_dmma_wgrad(const void* gz_bf16, const float* gz_f32, int cout, const void* a_bf16, int cin, float* dw,
+                              float* db, int B, int Hi, int Wi, int Ho, int Wo, int stride, void* stream) {
+  return dmma_wgrad_pitched(gz_bf16, gz_f32, cout, a_bf16, cin, dw, db, B, Hi, Wi, Hi, Wi, Ho, Wo, stride, stream);
 }
 
 extern "C" int srb_dl1_fwd(const float* img, const float* w, const float* bias, void* out_bf16, const void* ref, int C,

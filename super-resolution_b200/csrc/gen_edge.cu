@@ -341,11 +341,64 @@ extern "C" int srb_conv_in_bwd(const float* img, int B, int Cimg, int H, int W, 
   return 0;
 }
 
+// ---- conv3.2 on the warp-MMA kernels of csrc/disc_mma.cu (single image channel, 64 dense feature channels) ----
+// bf16 weight packs in the layouts those kernels read:  forward [9][8][64] (row 0 = the one output channel),
+// input gradient [9][64][16] (the 1-channel fp32 gradient is column 0; taps flipped).
+__device__ __nv_bfloat16 g_c32_wfwd[9 * 8 * 64];
+__device__ __nv_bfloat16 g_c32_wdg[9 * 64 * 16];
+
+__global__ void conv_out_pack_kernel(const float* __restrict__ w) {     // w: fp32 [1][64][3][3]
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 9 * 8 * 64 + 9 * 64 * 16; i += gridDim.x * blockDim.x) {
+    if (i < 9 * 8 * 64) {
+      const int k = i % 64, r = (i / 64) % 8, t = i / (64 * 8);
+      g_c32_wfwd[i] = __float2bfloat16(r == 0 ? w[k * 9 + t] : 0.f);
+    } else {
+      const int j = i - 9 * 8 * 64;
+      const int k = j % 16, ci = (j / 16) % 64, t = j / (16 * 64);
+      g_c32_wdg[j] = __float2bfloat16(k == 0 ? w[ci * 9 + (8 - t)] : 0.f);
+    }
+  }
+}
+
+// z = raw / multiplier and the output head (models.py:131-135), in place on `out` which holds the raw convolution
+__global__ void head_fwd_kernel(float* __restrict__ out, float* __restrict__ srs, float* __restrict__ z, long long n,
+                                float inv_multiplier, float power, float thres, int training) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float zz = out[i] * inv_multiplier;
+  if (z) z[i] = zz;
+  const float lam_p = powf(thres, power);
+  const float s = training ? zz : fmaxf(zz, 0.f);
+  srs[i] = hardshrink(s, lam_p);
+  float o2 = zz;
+  if (power != 1.f) o2 = powf(fmaxf(zz, 0.f), 1.f / power);
+  if (!training) o2 = fmaxf(o2, 0.f);
+  out[i] = hardshrink(o2, thres);
+}
+
+static bool conv_out_tc_ok(int Cimg, int F, int cstride, int coff, int W) {
+  return Cimg == 1 && F == 64 && cstride == 64 && coff == 0 && W >= 8;
+}
+
 extern "C" int srb_conv_out_fwd(const void* x, int x_cstride, int x_coff, int B, int H, int W, int F, const float* w,
                                 const float* bias, int Cimg, float multiplier, float power, float thres, int training,
                                 float* out, float* srs, float* z, void* stream) {
   if (F % 64) return set_error("conv_out: F must be a multiple of 64");
   if ((x_cstride % 8) || (x_coff % 8)) return set_error("conv_out: channel stride/offset must keep 16-byte alignment");
+  if (conv_out_tc_ok(Cimg, F, x_cstride, x_coff, W)) {
+    cudaStream_t st = (cudaStream_t)stream;
+    conv_out_pack_kernel<<<8, 256, 0, st>>>(w);
+    SRB_LAUNCH_CHECK("conv_out_pack");
+    void* wp = nullptr;
+    cudaGetSymbolAddress(&wp, g_c32_wfwd);
+    if (dmma_conv_pitched(x, nullptr, 64, wp, bias, 1, nullptr, out, nullptr, B, H, W, H, W, H + 1, W + 1, H, W, 1, 0, 0,
+                          0.f, stream))
+      return 1;
+    const long long n = 1LL * B * H * W;
+    head_fwd_kernel<<<ceil_div(n, 256), 256, 0, st>>>(out, srs, z, n, 1.f / multiplier, power, thres, training);
+    SRB_LAUNCH_CHECK("head_fwd");
+    return 0;
+  }
   const long long threads = 1LL * B * H * W * 8;
   const size_t wsm = sizeof(float) * Cimg * 9 * F;
   if (wsm > 48 * 1024) return set_error("conv_out: weights do not fit in shared memory");
@@ -365,6 +418,19 @@ extern "C" int srb_conv_out_bwd(const float* z, const float* g_out, const float*
   head_bwd_kernel<<<ceil_div(n, 256), 256, 0, st>>>(z, g_out, g_srs, n, 1.f / multiplier, power, thres, training,
                                                     gz_scratch);
   SRB_LAUNCH_CHECK("head_bwd");
+  if (conv_out_tc_ok(Cimg, F, act_cstride, act_coff, W) && gy_cstride == 64 && gy_coff == 0) {
+    conv_out_pack_kernel<<<8, 256, 0, st>>>(w);
+    SRB_LAUNCH_CHECK("conv_out_pack");
+    void* wp = nullptr;
+    cudaGetSymbolAddress(&wp, g_c32_wdg);
+    // input gradient = 3x3 convolution of the 1-channel gradient with the flipped taps, times LeakyReLU'(act)
+    if (dmma_conv_pitched(nullptr, gz_scratch, 1, wp, nullptr, 64, gy, nullptr, act, B, H, W, H, W, H, W, H + 1, W + 1, 1,
+                          0, 2, slope, stream))
+      return 1;
+    cudaMemsetAsync(dw, 0, sizeof(float) * F * 9, st);
+    cudaMemsetAsync(db, 0, sizeof(float), st);
+    return dmma_wgrad_pitched(nullptr, gz_scratch, 1, act, 64, dw, db, B, H, W, H + 1, W + 1, H, W, 1, stream);
+  }
   const long long total = 1LL * B * H * W * (F / 8);
   conv_out_dgrad_kernel<<<ceil_div(total, 256), 256, 0, st>>>(gz_scratch, B, Cimg, H, W, w, F,
                                                               (const __nv_bfloat16*)act, act_cstride, act_coff, slope,
