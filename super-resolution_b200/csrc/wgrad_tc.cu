@@ -13,12 +13,14 @@
 // Work item = (pair of input-channel blocks, dy, 64-wide output-channel block, K split).  Each CTA accumulates
 // its whole K range in 192 TMEM columns, then writes a partial [3 taps][128 ci][64 co] fp32 tile to the
 // workspace; a second kernel reduces the K splits, scales, and scatters to OIHW (state_dict layout).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "sm100.cuh"
 
 namespace srb {
 
-constexpr int kWgThreads = 224;                 // warp 0 TMA, warps 1-2 MMA issuers, warps 3-6 epilogue / bias sums
+constexpr int kWgThreads = 224;                 // warp 0 TMA, warps 1-2 MMA issuers, warps 3-6 epilogue
 constexpr int kWgIssuers = 2;
 constexpr int kWgKc = 64;                       // pixels per pipeline stage
 constexpr int kWgStages = 6;
@@ -37,7 +39,6 @@ struct WgradParams {
   int x_coff, gy_coff;
   float* ws;         // [splits][9][n_cp*128][cout]
   int base_offset_mode;
-  float* dbias;      // bias gradient (atomically accumulated by the cp == 0, dy == 0 work items) or null
   float alpha;
   int unshuffle;
 };
@@ -46,6 +47,7 @@ struct WgradParams {
 // a dense block) run as ONE launch: more work per CTA (fewer K splits, fewer partial tiles to reduce) and one
 // prologue / tail instead of five.
 constexpr int kWgMaxGroup = 8;
+constexpr int kWgColsumFloats = 2048;           // widest gradient buffer the bias pass handles (channels)
 struct WgradGroup {
   int n, splits;
   int unit_start[kWgMaxGroup + 1];   // first (cp, cb, dy) unit of every problem
@@ -80,12 +82,11 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   int c_end = c_begin + p.chunks_per_split;
   if (c_end > n_chunks_total) c_end = n_chunks_total;
   const int n_chunks = c_end > c_begin ? c_end - c_begin : 0;
-  const bool do_bias = p.dbias != nullptr && cp == 0 && dyi == 1;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_x);
     tma_prefetch_desc(&tmap_g);
-    for (int i = 0; i < kWgStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], kWgIssuers + (do_bias ? 4 : 0)); }
+    for (int i = 0; i < kWgStages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], kWgIssuers); }
     mbar_init(done, kWgIssuers);
     fence_mbar_init();
   }
@@ -143,33 +144,6 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
     const int row = lg * 32 + lane;               // M index = input channel within the pair
     const int ci = cp * 128 + row;
     const int cin_pad = p.n_cp * 128;
-    if (do_bias) {
-      // bias gradient = column sums of gy.  These warps idle during the main loop, so they read the gradient window
-      // of every stage straight out of (128B-swizzled) shared memory: rows 1..64 of the dy == 0 window are exactly the
-      // chunk's own pixels.  Warp lg sums 16 rows, lane = channel pair.
-      float s0 = 0.f, s1 = 0.f;
-      uint32_t s = 0, ph = 0;
-      const int pair = lane;
-      for (int c = 0; c < n_chunks; ++c) {
-        mbar_wait(&full[s], ph, 14);
-        const uint8_t* gw = smem + s * kWgStageBytes + kWgXBytes;
-#pragma unroll 4
-        for (int j = 0; j < 16; ++j) {
-          const int r = 1 + lg * 16 + j;
-          const uint32_t v = *reinterpret_cast<const uint32_t*>(gw + r * 128 + ((((pair >> 2) ^ (r & 7)) << 4) | ((pair & 3) << 2)));
-          s0 += bf16lo(v); s1 += bf16hi(v);
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[s]);
-        if (++s == kWgStages) { s = 0; ph ^= 1; }
-      }
-      const int cq = p.cout / 4;
-      const int co = cb * 64 + pair * 2;
-      const int d0 = p.unshuffle ? (4 * (co % cq) + co / cq) : co;
-      const int d1 = p.unshuffle ? (4 * ((co + 1) % cq) + (co + 1) / cq) : co + 1;
-      atomicAdd(p.dbias + d0, p.alpha * s0);
-      atomicAdd(p.dbias + d1, p.alpha * s1);
-    }
     if (n_chunks > 0) {
       mbar_wait(done, 0, 13);
       tc_fence_after();
@@ -209,7 +183,42 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
 
 // Sum the K splits, scale, and scatter to OIHW.  One thread per (t, ci, co); co fastest so workspace reads coalesce.
 // blockIdx.y selects the problem of the group.
-struct ReduceItem { const float* ws; float* dw; int cin, cin_pad, cout; float alpha; };
+// Bias gradients: column sums of the gradient buffer over all flat rows (pad rows are zero), every channel of the
+// buffer in one pass (the five convolutions of a dense block read adjacent 64-channel slices of it).  A thread owns
+// one 16-byte channel group and strides over rows; block partials go to `out` with atomics (zeroed by the caller).
+__global__ void __launch_bounds__(256)
+colsum_kernel(const __nv_bfloat16* __restrict__ g, long long R, int cstride, float* __restrict__ out) {
+  __shared__ float red[8 * 256];
+  pdl_trigger();
+  pdl_wait();
+  const int c8n = cstride >> 3;                       // 16-byte groups per row
+  const int rpb = 256 / c8n;                          // rows per block per step
+  const int ck = threadIdx.x % c8n, rr = threadIdx.x / c8n;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  if (rr < rpb) {
+    for (long long r = blockIdx.x * (long long)rpb + rr; r < R; r += (long long)gridDim.x * rpb) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(g + r * cstride) + ck);
+      acc[0] += bf16lo(v.x); acc[1] += bf16hi(v.x); acc[2] += bf16lo(v.y); acc[3] += bf16hi(v.y);
+      acc[4] += bf16lo(v.z); acc[5] += bf16hi(v.z); acc[6] += bf16lo(v.w); acc[7] += bf16hi(v.w);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red[i * 256 + threadIdx.x] = acc[i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < cstride; i += 256) {
+    const int k = i >> 3, e = i & 7;
+    float sum = 0.f;
+    for (int j = 0; j < rpb; ++j) sum += red[e * 256 + j * c8n + k];
+    atomicAdd(out + i, sum);
+  }
+}
+
+// Sum the K splits, scale, and scatter to OIHW.  One thread per (t, ci, co); co fastest so workspace reads coalesce.
+// blockIdx.y selects the problem of the group.  The first `cout` threads of blockIdx.x == 0 also finish the bias
+// gradient from the column sums.
+struct ReduceItem { const float* ws; float* dw; int cin, cin_pad, cout; float alpha; const float* colsum; float* dbias; };
 struct ReduceGroup { int n, splits, accumulate, unshuffle; ReduceItem it[kWgMaxGroup]; };
 
 __global__ void wgrad_reduce_kernel(const __grid_constant__ ReduceGroup rg) {
@@ -218,6 +227,14 @@ __global__ void wgrad_reduce_kernel(const __grid_constant__ ReduceGroup rg) {
   const long long total = 9LL * cin * cout;
   pdl_trigger();
   pdl_wait();
+  if (blockIdx.x == 0 && r_.dbias) {
+    for (int co = threadIdx.x; co < cout; co += blockDim.x) {
+      const int cq = cout / 4;
+      const int d = rg.unshuffle ? (4 * (co % cq) + co / cq) : co;
+      const float v = r_.alpha * r_.colsum[co];
+      r_.dbias[d] = rg.accumulate ? r_.dbias[d] + v : v;
+    }
+  }
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
     const int co = int(idx % cout);
     long long r = idx / cout;
@@ -258,7 +275,7 @@ static size_t wgrad_group_ws(int n, const int* cin, const int* cout, int splits,
     if (offs) offs[i] = total;
     total += static_cast<size_t>(splits) * 9 * ((cin[i] + 127) / 128) * 128 * cout[i];
   }
-  return total * sizeof(float);
+  return (total + kWgColsumFloats) * sizeof(float);   // + column sums of the gradient buffer (bias gradients)
 }
 
 int wgrad3x3_tc_launch_group(const srb_wgrad3x3_args* a, int n, cudaStream_t stream) {
@@ -291,6 +308,8 @@ int wgrad3x3_tc_launch_group(const srb_wgrad3x3_args* a, int n, cudaStream_t str
   if (make_tmap_2d_bf16(&tg, a0.gy, (uint64_t)a0.gy_cstride, (uint64_t)R, (uint64_t)a0.gy_cstride * 2, 64, kWgGRows)) return 1;
 
   g.n = n; g.splits = splits;
+  float* colsum = (float*)a0.workspace + (need / sizeof(float) - kWgColsumFloats);
+  bool any_bias = false;
   ReduceGroup rg{};
   rg.n = n; rg.splits = splits; rg.accumulate = a0.accumulate; rg.unshuffle = a0.unshuffle;
   long long max_total = 0;
@@ -301,11 +320,22 @@ int wgrad3x3_tc_launch_group(const srb_wgrad3x3_args* a, int n, cudaStream_t str
     p.n_cp = (ai.cin + 127) / 128; p.n_cb = ai.cout / 64;
     p.splits = splits; p.chunks_per_split = cps; p.x_coff = ai.x_coff; p.gy_coff = ai.gy_coff;
     p.ws = (float*)a0.workspace + offs[i]; p.base_offset_mode = 0;
-    p.dbias = ai.dbias; p.alpha = ai.alpha; p.unshuffle = ai.unshuffle;
-    if (ai.dbias && !ai.accumulate) cudaMemsetAsync(ai.dbias, 0, sizeof(float) * ai.cout, stream);
-    rg.it[i] = ReduceItem{p.ws, ai.dw, ai.cin, p.n_cp * 128, ai.cout, ai.alpha};
+    p.alpha = ai.alpha; p.unshuffle = ai.unshuffle;
+    rg.it[i] = ReduceItem{p.ws, ai.dw, ai.cin, p.n_cp * 128, ai.cout, ai.alpha,
+                          ai.dbias ? colsum + ai.gy_coff : nullptr, ai.dbias};
+    any_bias = any_bias || ai.dbias != nullptr;
     const long long tot = 9LL * ai.cin * ai.cout;
     if (tot > max_total) max_total = tot;
+  }
+  if (any_bias) {
+    if (a0.gy_cstride > kWgColsumFloats) return set_error("wgrad3x3: gradient buffer too wide for the bias pass");
+    cudaMemsetAsync(colsum, 0, sizeof(float) * a0.gy_cstride, stream);
+    const int rpb = 256 / (a0.gy_cstride / 8);
+    long long blocks = (R + rpb - 1) / rpb;
+    if (blocks > 8LL * sm_count()) blocks = 8LL * sm_count();
+    colsum_kernel<<<(unsigned)blocks, 256, 0, stream>>>((const __nv_bfloat16*)a0.gy, R, a0.gy_cstride, colsum);
+    cudaError_t ce = cudaGetLastError();
+    if (ce != cudaSuccess) return set_cuda_error("colsum launch", ce);
   }
   static bool attr = false;
   const size_t smem = 1024 + size_t(kWgStages) * kWgStageBytes + 256;
