@@ -22,7 +22,9 @@
 
 namespace srb {
 
-constexpr int kIgemmThreads = 288;   // warp 0 TMA producer, warps 1-4 MMA issuers, warps 5-8 epilogue
+constexpr int kIgemmThreads = 416;   // warp 0 TMA producer, warps 1-4 MMA issuers, warps 5-12 epilogue
+constexpr int kEpiWarps = 8;         // two per TMEM lane group: each takes 32 of a block's 64 columns, which doubles the
+                                     // mask / residual loads in flight (the K = 64 input-gradient convs are bound by them)
 constexpr int kIssuers = 4;
 constexpr int kBSlots = 4;           // weight ring: one slot = the three taps of one filter row (3 x 8 KB)
 constexpr int kAStages = 2;          // halo-window ring
@@ -93,7 +95,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     tma_prefetch_desc(&tmap_w);
     for (int i = 0; i < kAStages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], kIssuers); }
     for (int i = 0; i < kBSlots; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], kIssuers); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&t_full[i], kIssuers); mbar_init(&t_empty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&t_full[i], kIssuers); mbar_init(&t_empty[i], kEpiWarps); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
@@ -193,8 +195,9 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue warps 5..8
+    // ------------------------------------------------------------------ epilogue warps 5..12
     const int lg = warp & 3;                    // TMEM lane group this warp may access
+    const int half = (warp - 5) >> 2;           // which 32 of the 64 columns
     uint32_t as = 0, pt = 0;
     for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
       const int nt = work % p.n_ntiles;
@@ -223,8 +226,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
           yrow = static_cast<size_t>(q);
           ycoff += n0;
         }
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
+        {
           float v[32];
           {
             uint32_t acc[32];
