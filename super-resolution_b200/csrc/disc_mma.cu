@@ -390,6 +390,7 @@ dmma_wgrad_kernel(const DmmaWgradP p, const __grid_constant__ CUtensorMap tmap_a
   uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dsm) + 1023) & ~uintptr_t(1023));
   const int stage_bytes = p.a_bytes + p.g_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(ring + p.nst * stage_bytes);
+  int* ntab = reinterpret_cast<int*>(bars + kDwgMaxStages);      // [M16] activation-tile pixel of fragment row m, tap (0,0)
   const int S = p.stride;
   const int TR = p.TH * S + 2, TC = p.Wo * S + 2;
   const int M_img = p.TH * p.Wo;
@@ -398,6 +399,15 @@ dmma_wgrad_kernel(const DmmaWgradP p, const __grid_constant__ CUtensorMap tmap_a
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ky = warp / 3, kx = warp - ky * 3;
   const bool g_tma = p.gz_f32 == nullptr;
+  // the tile geometry is the same for every tile: do the index arithmetic once (rows >= M carry a zero gradient,
+  // any valid pixel will do)
+  for (int m = threadIdx.x; m < M16; m += kDwgThreads) {
+    const int mm = m < M ? m : 0;
+    const int im = mm / M_img;
+    const int rem = mm - im * M_img;
+    const int yl = rem / p.Wo, x = rem - yl * p.Wo;
+    ntab[m] = (im * TR + yl * S) * TC + x * S;
+  }
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -474,12 +484,7 @@ dmma_wgrad_kernel(const DmmaWgradP p, const __grid_constant__ CUtensorMap tmap_a
     const int kA = (lane & 7) + ((lane >> 4) << 3);
     const int kB = (lane & 7) + (((lane >> 3) & 1) << 3);
     for (int ch = 0; ch < M16 / 16; ++ch) {
-      int m = ch * 16 + kB;
-      if (m >= M) m = 0;                                  // gradient row is zero there: any finite input row will do
-      const int im = m / M_img;
-      const int rem = m - im * M_img;
-      const int yl = rem / p.Wo, x = rem - yl * p.Wo;
-      const int n = (im * TR + yl * S + ky) * TC + x * S + kx;
+      const int n = ntab[ch * 16 + kB] + ky * TC + kx;
       const uint32_t brow = a_u32 + n * PA;
       const int swb = (n >> SHA) & SWA;
       const int r = ch * 16 + kA;
@@ -879,7 +884,7 @@ static int dmma_conv_launch_n(DmmaConvP& p, cudaStream_t st) {
 template <int KS, int MT>
 static int dmma_wgrad_launch_t(DmmaWgradP& p, cudaStream_t st) {
   constexpr int PA = KS * 32, PG = MT * 32;
-  const size_t fixed = kDwgMaxStages * 8 + 1024;
+  const size_t fixed = kDwgMaxStages * 8 + 1024 + 272 * 4;      // barriers, alignment slack, pixel table (M16 <= 272)
   int TH = 0, IMGS = 0, TR = 0, TC = 0, nst = 2;
   size_t a_bytes = 0, g_bytes = 0, smem = 0;
   bool ok = false;
@@ -908,6 +913,7 @@ static int dmma_wgrad_launch_t(DmmaWgradP& p, cudaStream_t st) {
     }
   }
   if (!ok) return set_error("dmma_wgrad: tile does not fit in shared memory");
+  if (((IMGS * TH * p.Wo + 15) & ~15) > 272) return set_error("dmma_wgrad: map wider than 256 pixels");
   p.TH = TH; p.IMGS = IMGS; p.nst = nst; p.a_bytes = int(a_bytes); p.g_bytes = int(g_bytes);
   p.tiles_y = (p.Ho + TH - 1) / TH;
   p.n_tiles = p.tiles_y * ((p.B + IMGS - 1) / IMGS);
