@@ -17,6 +17,8 @@
 //   of tile i+1.  Persistent CTAs, static round-robin tile schedule.
 // Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2..5 = epilogue
 //   (TMEM -> registers -> bias/scale/residual/activation -> bf16 global stores).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "sm100.cuh"
 
@@ -59,6 +61,93 @@ __device__ __forceinline__ void load_row64(const __nv_bfloat16* p, uint4 (&v)[8]
   const uint4* q = reinterpret_cast<const uint4*>(p);
 #pragma unroll
   for (int i = 0; i < 8; ++i) v[i] = __ldg(q + i);
+}
+
+// Per-row epilogue shared by the tcgen05 convolution kernels: v[32] = fp32 accumulators of flat row q, output channels
+// [nt*64 + half*32, +32) -> bias, alpha, residual streams, LeakyReLU / LeakyReLU' mask -> bf16 store (plain or
+// PixelShuffle-addressed).  Called for valid pixels only.
+__device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)[32], int q, int py, int px, int nt,
+                                                int half) {
+  const int n0 = nt * 64;
+  size_t yrow;
+  int ycoff = p.y_coff;
+  if (p.store_mode == SRB_STORE_SHUFFLE) {
+    const int img = q / p.P;
+    const int cblocks = p.n_ntiles >> 2;  // 64-wide blocks per shuffled output channel group (Cy / 64)
+    const int sub = nt / cblocks;         // (i,j) = (sub>>1, sub&1)
+    yrow = static_cast<size_t>(img) * p.y_P + static_cast<size_t>(2 * py + (sub >> 1)) * p.y_pitch +
+           (2 * px + (sub & 1));
+    ycoff += (nt % cblocks) * 64;
+  } else {
+    yrow = static_cast<size_t>(q);
+    ycoff += n0;
+  }
+  const int c0 = n0 + half * 32;
+  if (p.bias) {
+    const float4* b4 = reinterpret_cast<const float4*>(p.bias + c0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 b = __ldg(b4 + i);
+      v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] *= p.alpha;
+  if (p.res1) {
+    const uint4* rp = reinterpret_cast<const uint4*>(p.res1 + static_cast<size_t>(q) * p.res1_cstride +
+                                                     p.res1_coff + c0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint4 u = __ldg(rp + i);
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[8 * i + 2 * j] += p.res1_scale * bf16lo(w[j]);
+        v[8 * i + 2 * j + 1] += p.res1_scale * bf16hi(w[j]);
+      }
+    }
+  }
+  if (p.res2) {
+    const uint4* rp = reinterpret_cast<const uint4*>(p.res2 + static_cast<size_t>(q) * p.res2_cstride +
+                                                     p.res2_coff + c0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint4 u = __ldg(rp + i);
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[8 * i + 2 * j] += p.res2_scale * bf16lo(w[j]);
+        v[8 * i + 2 * j + 1] += p.res2_scale * bf16hi(w[j]);
+      }
+    }
+  }
+  if (p.act == SRB_ACT_LRELU) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.slope;
+  } else if (p.act == SRB_ACT_LRELU_MASK) {
+    const uint4* mp = reinterpret_cast<const uint4*>(p.mask + static_cast<size_t>(q) * p.mask_cstride +
+                                                     p.mask_coff + c0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint4 u = __ldg(mp + i);
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[8 * i + 2 * j] *= bf16lo(w[j]) > 0.f ? 1.f : p.slope;
+        v[8 * i + 2 * j + 1] *= bf16hi(w[j]) > 0.f ? 1.f : p.slope;
+      }
+    }
+  }
+  uint4* yp = reinterpret_cast<uint4*>(p.y + yrow * p.y_cstride + ycoff + half * 32);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    uint4 o;
+    o.x = pack_bf16(v[8 * i], v[8 * i + 1]);
+    o.y = pack_bf16(v[8 * i + 2], v[8 * i + 3]);
+    o.z = pack_bf16(v[8 * i + 4], v[8 * i + 5]);
+    o.w = pack_bf16(v[8 * i + 6], v[8 * i + 7]);
+    yp[i] = o;
+  }
 }
 
 // dbg bit 8: CTA 0 records clock64 stamps of its pipeline (tools/exp_conv.py reads them back)
@@ -211,106 +300,22 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
         const int py = r / p.pitch, px = r - py * p.pitch;
         const bool valid = (q < p.R) && (px < p.W) && (py < p.H) && !(p.dbg & 4);
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + as * 256 + mt * (NACC * 64);
-        const int n0 = nt * 64;
-        // destination row
-        size_t yrow;
-        int ycoff = p.y_coff;
-        if (p.store_mode == SRB_STORE_SHUFFLE) {
-          const int img = q / p.P;
-          const int cblocks = p.n_ntiles >> 2;  // 64-wide blocks per shuffled output channel group (Cy / 64)
-          const int sub = nt / cblocks;         // (i,j) = (sub>>1, sub&1)
-          yrow = static_cast<size_t>(img) * p.y_P + static_cast<size_t>(2 * py + (sub >> 1)) * p.y_pitch +
-                 (2 * px + (sub & 1));
-          ycoff += (nt % cblocks) * 64;
-        } else {
-          yrow = static_cast<size_t>(q);
-          ycoff += n0;
-        }
+        float v[32];
         {
-          float v[32];
-          {
-            uint32_t acc[32];
-            tmem_ld32(taddr + half * 32, acc);
+          uint32_t acc[32];
+          tmem_ld32(taddr + half * 32, acc);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]);
+#pragma unroll
+          for (int j = 1; j < NACC; ++j) {
+            tmem_ld32(taddr + j * 64 + half * 32, acc);
             tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]);
-#pragma unroll
-            for (int j = 1; j < NACC; ++j) {
-              tmem_ld32(taddr + j * 64 + half * 32, acc);
-              tmem_ld_wait();
-#pragma unroll
-              for (int i = 0; i < 32; ++i) v[i] += __uint_as_float(acc[i]);
-            }
-          }
-          if (valid) {
-            const int c0 = n0 + half * 32;
-            if (p.bias) {
-              const float4* b4 = reinterpret_cast<const float4*>(p.bias + c0);
-#pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                const float4 b = __ldg(b4 + i);
-                v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
-              }
-            }
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] *= p.alpha;
-            if (p.res1) {
-              const uint4* rp = reinterpret_cast<const uint4*>(p.res1 + static_cast<size_t>(q) * p.res1_cstride +
-                                                               p.res1_coff + c0);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint4 u = __ldg(rp + i);
-                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  v[8 * i + 2 * j] += p.res1_scale * bf16lo(w[j]);
-                  v[8 * i + 2 * j + 1] += p.res1_scale * bf16hi(w[j]);
-                }
-              }
-            }
-            if (p.res2) {
-              const uint4* rp = reinterpret_cast<const uint4*>(p.res2 + static_cast<size_t>(q) * p.res2_cstride +
-                                                               p.res2_coff + c0);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint4 u = __ldg(rp + i);
-                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  v[8 * i + 2 * j] += p.res2_scale * bf16lo(w[j]);
-                  v[8 * i + 2 * j + 1] += p.res2_scale * bf16hi(w[j]);
-                }
-              }
-            }
-            if (p.act == SRB_ACT_LRELU) {
-#pragma unroll
-              for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.slope;
-            } else if (p.act == SRB_ACT_LRELU_MASK) {
-              const uint4* mp = reinterpret_cast<const uint4*>(p.mask + static_cast<size_t>(q) * p.mask_cstride +
-                                                               p.mask_coff + c0);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint4 u = __ldg(mp + i);
-                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  v[8 * i + 2 * j] *= bf16lo(w[j]) > 0.f ? 1.f : p.slope;
-                  v[8 * i + 2 * j + 1] *= bf16hi(w[j]) > 0.f ? 1.f : p.slope;
-                }
-              }
-            }
-            uint4* yp = reinterpret_cast<uint4*>(p.y + yrow * p.y_cstride + ycoff + half * 32);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              uint4 o;
-              o.x = pack_bf16(v[8 * i], v[8 * i + 1]);
-              o.y = pack_bf16(v[8 * i + 2], v[8 * i + 3]);
-              o.z = pack_bf16(v[8 * i + 4], v[8 * i + 5]);
-              o.w = pack_bf16(v[8 * i + 6], v[8 * i + 7]);
-              yp[i] = o;
-            }
+            for (int i = 0; i < 32; ++i) v[i] += __uint_as_float(acc[i]);
           }
         }
+        if (valid) igemm_store_row(p, v, q, py, px, nt, half);
       }
       tc_fence_before();
       __syncwarp();
@@ -330,6 +335,12 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 }
 
 // ---------------------------------------------------------------------------------- host side
+int conv3x3_row_launch(const srb_conv3x3_args* a, cudaStream_t stream);     // conv_row.cu
+static bool conv_row_enabled() {       // SRB_CONV_ROW=0 keeps the one-tap-per-MMA kernel (A/B timing)
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("SRB_CONV_ROW"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
 static size_t igemm_smem_bytes(uint32_t a_stage_bytes) {
   return 1024 + size_t(kAStages) * a_stage_bytes + size_t(kBSlots) * kBSlotBytes + 512;
 }
@@ -343,6 +354,10 @@ int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   const long long R = 1LL * a->batch * P;
   if (R <= 0 || R > 0x7fffffffLL) return set_error("conv3x3: bad geometry");
   const int halo = pitch + 1;
+  if (conv_row_enabled() && (a->flags >> 1) == 0) {       // filter-row kernel (conv_row.cu); -1: geometry does not fit
+    const int rc = conv3x3_row_launch(a, stream);
+    if (rc >= 0) return rc;
+  }
 
   // tile height: two 128-row sub-tiles per CTA when that still fills the machine
   const int sms = sm_count();
