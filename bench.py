@@ -317,7 +317,14 @@ def run_ours(args):
         }
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # The NCCL all-reduces live inside the captured CUDA graph; tearing the communicator down with
+        # destroy_process_group() after graph replays was seen to hang (session 27, 2 GPUs) although every rank had
+        # finished.  All results are printed by now: agree that everyone is done, then leave without the teardown.
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":

@@ -336,9 +336,11 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 
 // ---------------------------------------------------------------------------------- host side
 int conv3x3_row_launch(const srb_conv3x3_args* a, cudaStream_t stream);     // conv_row.cu
-static bool conv_row_enabled() {       // SRB_CONV_ROW=0 keeps the one-tap-per-MMA kernel (A/B timing)
+// Kernel choice: the one-tap-per-MMA kernel below is the default; SRB_CONV_ROW=1 (read once per process) or flags bit
+// 16 selects the filter-row kernel, flags bit 17 forces the one-tap kernel (tests run both on the same inputs).
+static bool conv_row_enabled() {
   static int v = -1;
-  if (v < 0) { const char* e = getenv("SRB_CONV_ROW"); v = (e && e[0] == '0') ? 0 : 1; }
+  if (v < 0) { const char* e = getenv("SRB_CONV_ROW"); v = (e && e[0] == '1') ? 1 : 0; }
   return v != 0;
 }
 static size_t igemm_smem_bytes(uint32_t a_stage_bytes) {
@@ -354,7 +356,8 @@ int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   const long long R = 1LL * a->batch * P;
   if (R <= 0 || R > 0x7fffffffLL) return set_error("conv3x3: bad geometry");
   const int halo = pitch + 1;
-  if (conv_row_enabled() && (a->flags >> 1) == 0) {       // filter-row kernel (conv_row.cu); -1: geometry does not fit
+  const bool want_row = (a->flags & 0x10000) || (conv_row_enabled() && !(a->flags & 0x20000));
+  if (want_row && ((a->flags >> 1) & 0x7fff) == 0) {      // filter-row kernel (conv_row.cu); -1: geometry does not fit
     const int rc = conv3x3_row_launch(a, stream);
     if (rc >= 0) return rc;
   }
@@ -398,7 +401,7 @@ int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   p.res1 = (const __nv_bfloat16*)a->res1; p.res1_cstride = a->res1_cstride; p.res1_coff = a->res1_coff; p.res1_scale = a->res1_scale;
   p.res2 = (const __nv_bfloat16*)a->res2; p.res2_cstride = a->res2_cstride; p.res2_coff = a->res2_coff; p.res2_scale = a->res2_scale;
   p.base_offset_mode = a->flags & 1;
-  p.dbg = a->flags >> 1;
+  p.dbg = (a->flags >> 1) & 0x7fff;
   if (p.act == SRB_ACT_LRELU_MASK && !p.mask) return set_error("conv3x3: mask activation without mask tensor");
 
   const int grid = p.num_work < sms ? p.num_work : sms;
