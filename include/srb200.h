@@ -76,6 +76,18 @@ typedef struct srb_conv3x3_args {
 
 int srb_conv3x3(const srb_conv3x3_args* a, void* stream);
 
+/* A chain of n (<= SRB_CONV_CHAIN_MAX) such convolutions over the same pixel grid in ONE persistent launch
+ * (csrc/conv_chain.cu): layer l may read anything layers < l of the chain wrote - the five convolutions of a
+ * DenseResidualBlock (models.py:34-41), the three dense blocks of an RRDB (models.py:52-53), or the input-gradient
+ * chain of a dense block.  All layers share batch, H, W and cout, store plainly and use the tcgen05 kernels.  A tile
+ * of layer l starts when the neighbouring tiles of layer l-1 are complete (per-tile counters in `flags`), so the
+ * tensor pipe does not drain between layers.  `flags`: device workspace of srb_conv3x3_chain_flag_bytes(...) bytes,
+ * ZERO on entry (the caller clears it; one workspace per chain launch in flight).  Results are identical to n
+ * srb_conv3x3 calls in order. */
+#define SRB_CONV_CHAIN_MAX 16
+int srb_conv3x3_chain(const srb_conv3x3_args* layers, int n, void* flags, size_t flag_bytes, void* stream);
+size_t srb_conv3x3_chain_flag_bytes(int batch, int H, int W, int n);
+
 /* Weight packing, fp32 OIHW -> bf16 [9][cin/64][cout][64].
  *   mode 0 (forward):  wp[t][kb][n][k] = w[perm(n)][kb*64+k][t] * scale
  *   mode 1 (dgrad)  :  treats `w` as the forward weight [co][ci_total][3][3]; produces the pack of the

@@ -66,6 +66,12 @@ __device__ __forceinline__ void load_row64(const __nv_bfloat16* p, uint4 (&v)[8]
 // Per-row epilogue shared by the tcgen05 convolution kernels: v[32] = fp32 accumulators of flat row q, output channels
 // [nt*64 + half*32, +32) -> bias, alpha, residual streams, LeakyReLU / LeakyReLU' mask -> bf16 store (plain or
 // PixelShuffle-addressed).  Called for valid pixels only.
+// COHERENT = true reads the residual / mask streams with ld.global.cg instead of the non-coherent path: the chained
+// kernel (conv_chain.cu) reads rows that an earlier layer of the SAME launch wrote.
+template <bool COHERENT>
+__device__ __forceinline__ uint4 ld_row16(const uint4* p) { return COHERENT ? __ldcg(p) : __ldg(p); }
+
+template <bool COHERENT = false>
 __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)[32], int q, int py, int px, int nt,
                                                 int half) {
   const int n0 = nt * 64;
@@ -98,7 +104,7 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
                                                      p.res1_coff + c0);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const uint4 u = __ldg(rp + i);
+      const uint4 u = ld_row16<COHERENT>(rp + i);
       const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -112,7 +118,7 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
                                                      p.res2_coff + c0);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const uint4 u = __ldg(rp + i);
+      const uint4 u = ld_row16<COHERENT>(rp + i);
       const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -129,7 +135,7 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
                                                      p.mask_coff + c0);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const uint4 u = __ldg(mp + i);
+      const uint4 u = ld_row16<COHERENT>(mp + i);
       const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -158,11 +164,12 @@ __global__ void __launch_bounds__(kIgemmThreads, 1)
 conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
                      const IgemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
+  constexpr int NB = MT == 4 ? 3 : kBSlots;     // weight ring slots (MT == 4: two 512-row windows leave room for three)
   // carve: [A stages][B slots][barriers]
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* a_smem = smem;
   uint8_t* b_smem = a_smem + kAStages * p.a_stage_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(b_smem + kBSlots * kBSlotBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(b_smem + NB * kBSlotBytes);
   uint64_t* a_full = bars;                      // [kAStages]
   uint64_t* a_empty = a_full + kAStages;        // [kAStages]
   uint64_t* b_full = a_empty + kAStages;        // [kBSlots]
@@ -200,7 +207,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync: ptxas then keeps descriptors and barrier addresses in uniform registers
       uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
       for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
         const int nt = work % p.n_ntiles;
@@ -225,7 +232,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
                 tma_load_2d(b_smem + sb * kBSlotBytes + dx * kBTileBytes, &tmap_w, 0,
                             ((dy * 3 + dx) * p.KB + kb) * p.cout + nt * 64, &b_full[sb]);
             }
-            if (++sb == kBSlots) { sb = 0; pb ^= 1; }
+            if (++sb == NB) { sb = 0; pb ^= 1; }
           }
         }
       }
@@ -236,12 +243,13 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     // barrier traffic, but a 128x64x16 MMA only occupies the tensor pipe for 32 clk (tools/probe1.py rate).  So the
     // issue work is split over four warps on four different schedulers.  MMAs from different threads are unordered,
     // hence every issuer owns a private 64-column accumulator (no "first MMA clears" hazard); the epilogue adds them.
+    //   MT == 4: issuer i -> sub-tile i, all four k-steps (one accumulator per sub-tile, nothing to add);
     //   MT == 2: issuer i -> sub-tile i >> 1, k-steps {2(i&1), 2(i&1)+1};   MT == 1: issuer i -> k-step i.
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync: ptxas then keeps descriptors and barrier addresses in uniform registers
       const int iss = warp - 1;
-      const int mt = MT == 2 ? (iss >> 1) : 0;
-      const int k0 = MT == 2 ? 2 * (iss & 1) : iss;
-      constexpr int NK = MT == 2 ? 2 : 1;
+      const int mt = MT == 4 ? iss : (MT == 2 ? (iss >> 1) : 0);
+      const int k0 = MT == 4 ? 0 : (MT == 2 ? 2 * (iss & 1) : iss);
+      constexpr int NK = MT == 4 ? 4 : (MT == 2 ? 2 : 1);
       constexpr uint32_t idesc = make_idesc_bf16(128, 64, 0, 0);
       constexpr uint64_t desc_hi = (uint64_t(16 >> 4) << 16) | (uint64_t(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
       const uint32_t a0 = ((smem_u32(a_smem) & 0x3FFFFu) >> 4) + mt * 1024 + k0 * 2;
@@ -273,7 +281,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             }
             umma_commit(&b_empty[sb]);
             row16 += static_cast<uint32_t>(p.pitch) * 8u;
-            if (++sb == kBSlots) { sb = 0; pb ^= 1; }
+            if (++sb == NB) { sb = 0; pb ^= 1; }
           }
           umma_commit(&a_empty[sa]);
           if (kb == p.KB - 1) umma_commit(&t_full[as]);
@@ -343,55 +351,87 @@ static bool conv_row_enabled() {
   if (v < 0) { const char* e = getenv("SRB_CONV_ROW"); v = (e && e[0] == '1') ? 1 : 0; }
   return v != 0;
 }
-static size_t igemm_smem_bytes(uint32_t a_stage_bytes) {
-  return 1024 + size_t(kAStages) * a_stage_bytes + size_t(kBSlots) * kBSlotBytes + 512;
+static size_t igemm_smem_bytes(uint32_t a_stage_bytes, int MT) {
+  return 1024 + size_t(kAStages) * a_stage_bytes + size_t(MT == 4 ? 3 : kBSlots) * kBSlotBytes + 512;
+}
+// SRB_CONV_MT4=0 (read once per process) keeps the 512-row tiles off.
+static bool conv_mt4_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("SRB_CONV_MT4"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
 }
 
-int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
+// Geometry-dependent part of a launch (shared by every layer of a chained launch, conv_chain.cu).
+struct IgemmPlan {
+  int MT, rows_tile, box_rows, nbox, n_mtiles;
+  uint32_t a_stage_bytes;
+  size_t smem;
+  long long R;
+};
+
+int igemm_check_args(const srb_conv3x3_args* a) {
   if (a->cin % 64 || a->cout % 64 || a->cin <= 0 || a->cout <= 0) return set_error("conv3x3: channels must be multiples of 64");
   if ((a->x_cstride % 8) || (a->y_cstride % 8) || (a->x_coff % 64) || (a->y_coff % 8))
     return set_error("conv3x3: channel strides/offsets must keep 16-byte alignment");
   if (a->store_mode == SRB_STORE_SHUFFLE && a->cout % 256) return set_error("conv3x3: shuffle store needs cout % 256 == 0");
+  const long long R = 1LL * a->batch * (a->H + 1) * (a->W + 1);
+  if (R <= 0 || R > 0x7fffffffLL) return set_error("conv3x3: bad geometry");
+  return 0;
+}
+
+// Tile height.  Every (tile, 64-channel k-block) step re-reads the k-block's nine weight tiles (72 KB) from L2 next to
+// the halo window of the tile (37 KB per 256 rows): at 256 rows per tile the weights are two thirds of the L2 -> SM
+// traffic, and that traffic (7.6 TB/s at the marginal rate) bounds the kernel.  512-row tiles (MT = 4: one issuer and
+// one accumulator per 128-row sub-tile) halve the weight traffic per pixel and drop the partial-accumulator adds of the
+// epilogue; they are used when the two windows fit next to a three-slot weight ring (LR geometries) and the coarser
+// tiles still fill the machine about as evenly.  Otherwise two 128-row sub-tiles per CTA when that fills the machine,
+// else one.  flags bit 18 forbids, bit 19 forces (if it fits) the 512-row tiles.
+static bool igemm_geom(const srb_conv3x3_args* a, int MT, IgemmPlan* pl) {
   const int pitch = a->W + 1, P = (a->H + 1) * (a->W + 1);
   const long long R = 1LL * a->batch * P;
-  if (R <= 0 || R > 0x7fffffffLL) return set_error("conv3x3: bad geometry");
   const int halo = pitch + 1;
-  const bool want_row = (a->flags & 0x10000) || (conv_row_enabled() && !(a->flags & 0x20000));
-  if (want_row && ((a->flags >> 1) & 0x7fff) == 0) {      // filter-row kernel (conv_row.cu); -1: geometry does not fit
-    const int rc = conv3x3_row_launch(a, stream);
-    if (rc >= 0) return rc;
-  }
+  const int rows_tile = 128 * MT;
+  const int win = rows_tile + 2 * halo;
+  const int win8 = (win + 7) & ~7;
+  const int nbox = (win8 + 255) / 256;
+  const int box_rows = (((win8 + nbox - 1) / nbox) + 7) & ~7;
+  pl->MT = MT; pl->rows_tile = rows_tile; pl->box_rows = box_rows; pl->nbox = nbox;
+  pl->a_stage_bytes = uint32_t(nbox) * box_rows * 128;
+  pl->smem = igemm_smem_bytes(pl->a_stage_bytes, MT);
+  pl->R = R;
+  pl->n_mtiles = int((R + rows_tile - 1) / rows_tile);
+  return pl->smem <= 227 * 1024;
+}
 
-  // tile height: two 128-row sub-tiles per CTA when that still fills the machine
+int igemm_make_plan(const srb_conv3x3_args* a, IgemmPlan* pl) {
   const int sms = sm_count();
   const int n_ntiles = a->cout / 64;
-  int MT = 2;
-  if (((R + 255) / 256) * n_ntiles < sms) MT = 1;
-  int rows_tile = 128 * MT;
-  int win = rows_tile + 2 * halo;
-  int win8 = (win + 7) & ~7;
-  int nbox = (win8 + 255) / 256;
-  int box_rows = (((win8 + nbox - 1) / nbox) + 7) & ~7;
-  uint32_t a_stage_bytes = uint32_t(nbox) * box_rows * 128;
-  size_t smem = igemm_smem_bytes(a_stage_bytes);
-  if (smem > 227 * 1024 && MT == 2) {
-    MT = 1; rows_tile = 128; win = rows_tile + 2 * halo; win8 = (win + 7) & ~7;
-    nbox = (win8 + 255) / 256; box_rows = (((win8 + nbox - 1) / nbox) + 7) & ~7;
-    a_stage_bytes = uint32_t(nbox) * box_rows * 128; smem = igemm_smem_bytes(a_stage_bytes);
-  }
-  if (smem > 227 * 1024) return set_error("conv3x3: image too wide for the tcgen05 kernel (W <= ~400)");
+  auto fill = [&](const IgemmPlan& q) {       // fraction of CTA-slots doing work over the launch's waves
+    const long long work = 1LL * q.n_mtiles * n_ntiles;
+    return double(work) / double(((work + sms - 1) / sms) * sms);
+  };
+  IgemmPlan p4, p2;
+  const bool fit4 = igemm_geom(a, 4, &p4), fit2 = igemm_geom(a, 2, &p2);
+  const bool allow4 = fit4 && !(a->flags & 0x40000) && (conv_mt4_enabled() || (a->flags & 0x80000));
+  if (allow4 && ((a->flags & 0x80000) ||
+                 (1LL * p4.n_mtiles * n_ntiles >= sms && fill(p4) >= fill(p2) - 0.04))) { *pl = p4; return 0; }
+  if (fit2 && 1LL * p2.n_mtiles * n_ntiles >= sms) { *pl = p2; return 0; }
+  if (!igemm_geom(a, 1, pl)) return set_error("conv3x3: image too wide for the tcgen05 kernel (W <= ~400)");
+  return 0;
+}
 
-  CUtensorMap tx, tw;
-  if (make_tmap_2d_bf16(&tx, a->x, (uint64_t)a->x_cstride, (uint64_t)R, (uint64_t)a->x_cstride * 2, 64, box_rows))
+// Per-layer part: tensor maps and kernel parameters of one convolution under plan `pl`.
+int igemm_fill(const srb_conv3x3_args* a, const IgemmPlan& pl, IgemmParams* pp, CUtensorMap* tx, CUtensorMap* tw) {
+  const int pitch = a->W + 1, P = (a->H + 1) * (a->W + 1);
+  if (make_tmap_2d_bf16(tx, a->x, (uint64_t)a->x_cstride, (uint64_t)pl.R, (uint64_t)a->x_cstride * 2, 64, pl.box_rows))
     return 1;
-  if (make_tmap_2d_bf16(&tw, a->w, 64, (uint64_t)9 * (a->cin / 64) * a->cout, 128, 64, 64)) return 1;
-
+  if (make_tmap_2d_bf16(tw, a->w, 64, (uint64_t)9 * (a->cin / 64) * a->cout, 128, 64, 64)) return 1;
   IgemmParams p{};
-  p.R = (int)R; p.P = P; p.pitch = pitch; p.H = a->H; p.W = a->W;
-  p.KB = a->cin / 64; p.cout = a->cout; p.n_ntiles = n_ntiles;
-  const int n_mtiles = int((R + rows_tile - 1) / rows_tile);
-  p.num_work = n_mtiles * n_ntiles;
-  p.x_coff = a->x_coff; p.halo = halo; p.a_box_rows = box_rows; p.a_nbox = nbox; p.a_stage_bytes = a_stage_bytes;
+  p.R = (int)pl.R; p.P = P; p.pitch = pitch; p.H = a->H; p.W = a->W;
+  p.KB = a->cin / 64; p.cout = a->cout; p.n_ntiles = a->cout / 64;
+  p.num_work = pl.n_mtiles * p.n_ntiles;
+  p.x_coff = a->x_coff; p.halo = pitch + 1; p.a_box_rows = pl.box_rows; p.a_nbox = pl.nbox;
+  p.a_stage_bytes = pl.a_stage_bytes;
   p.bias = a->bias;
   p.y = (__nv_bfloat16*)a->y; p.y_cstride = a->y_cstride; p.y_coff = a->y_coff; p.store_mode = a->store_mode;
   if (a->store_mode == SRB_STORE_SHUFFLE) { p.y_pitch = 2 * a->W + 1; p.y_P = (2 * a->H + 1) * (2 * a->W + 1); }
@@ -403,10 +443,31 @@ int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   p.base_offset_mode = a->flags & 1;
   p.dbg = (a->flags >> 1) & 0x7fff;
   if (p.act == SRB_ACT_LRELU_MASK && !p.mask) return set_error("conv3x3: mask activation without mask tensor");
+  *pp = p;
+  return 0;
+}
 
+int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
+  if (int rc = igemm_check_args(a)) return rc;
+  const bool want_row = (a->flags & 0x10000) || (conv_row_enabled() && !(a->flags & 0x20000));
+  if (want_row && ((a->flags >> 1) & 0x7fff) == 0) {      // filter-row kernel (conv_row.cu); -1: geometry does not fit
+    const int rc = conv3x3_row_launch(a, stream);
+    if (rc >= 0) return rc;
+  }
+  IgemmPlan pl;
+  if (int rc = igemm_make_plan(a, &pl)) return rc;
+  CUtensorMap tx, tw;
+  IgemmParams p;
+  if (int rc = igemm_fill(a, pl, &p, &tx, &tw)) return rc;
+  const int sms = sm_count();
   const int grid = p.num_work < sms ? p.num_work : sms;
+  const size_t smem = pl.smem;
   cudaError_t e;
-  if (MT == 2) {
+  if (pl.MT == 4) {
+    static bool attr4 = false;
+    if (!attr4) { cudaFuncSetAttribute(conv3x3_igemm_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr4 = true; }
+    e = launch_pdl(conv3x3_igemm_kernel<4>, dim3(grid), dim3(kIgemmThreads), smem, stream, tx, tw, p);
+  } else if (pl.MT == 2) {
     static bool attr2 = false;
     if (!attr2) { cudaFuncSetAttribute(conv3x3_igemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr2 = true; }
     e = launch_pdl(conv3x3_igemm_kernel<2>, dim3(grid), dim3(kIgemmThreads), smem, stream, tx, tw, p);

@@ -183,7 +183,7 @@ conv3x3_row_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync: ptxas then keeps descriptors and barrier addresses in uniform registers
       uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
       int na = 0, nb = 0;                        // loads issued so far (timing experiments, p.dbg)
       for (long long u = u_begin; u < u_end;) {
@@ -226,7 +226,7 @@ conv3x3_row_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
     // against the 96 clk a 128x192x16 MMA takes), so each sub-tile has its own issuer with its own accumulator.  Both
     // walk the same ring positions and both arrive on the slot / stage "empty" barriers (count 2); an issuer whose
     // sub-tile does not exist in a tile (odd tail of the CTA's range) walks the rings without issuing.
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync: ptxas then keeps descriptors and barrier addresses in uniform registers
       const int mt = warp - 1;
       constexpr uint32_t idesc = make_idesc_bf16(128, 192, 0, 0);
       constexpr uint32_t desc_hi32 = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO 1024, version 1, SWIZZLE_128B

@@ -99,7 +99,7 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   pdl_wait();
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync: ptxas then keeps descriptors and barrier addresses in uniform registers
       uint32_t s = 0, ph = 0;
       for (int c = 0; c < n_chunks; ++c) {
         const int k0 = (c_begin + c) * kWgKc;
@@ -115,7 +115,7 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   } else if (warp <= kWgIssuers) {
     // two issuer threads (see conv_igemm.cu): issuer i takes k-steps {2i, 2i+1} of every 64-pixel chunk and owns a
     // private 192-column accumulator; the epilogue adds the two.
-    if (lane == 0) {
+    if (elect_one()) {   // elect.sync: ptxas then keeps descriptors and barrier addresses in uniform registers
       constexpr uint32_t idesc = make_idesc_bf16(128, 192, 1, 1);
       constexpr uint64_t a_hi = (uint64_t((kWgKc * 128) >> 4) << 16) | (uint64_t(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
       constexpr uint64_t b_hi = (uint64_t(128 >> 4) << 16) | (uint64_t(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);

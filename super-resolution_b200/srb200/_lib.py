@@ -91,6 +91,8 @@ _SIGS = {
     "srb_abi_version": (C.c_int, []),
     "srb_read_fault": (C.c_int, [C.POINTER(C.c_uint)]),
     "srb_conv3x3": (C.c_int, [C.POINTER(Conv3x3Args), C.c_void_p]),
+    "srb_conv3x3_chain": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "srb_conv3x3_chain_flag_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "srb_pack_conv3x3_fwd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
     "srb_pack_conv3x3_dgrad": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                          C.c_void_p, C.c_int, C.c_int, C.c_void_p]),

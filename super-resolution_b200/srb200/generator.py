@@ -15,6 +15,7 @@ kernel launches over preallocated PNHWC bf16 buffers:
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -38,6 +39,33 @@ class _Bufs:
     pass
 
 
+class _FlagArena:
+    """Per-tile completion counters of the chained convolution launches (csrc/conv_chain.cu): every chain launch of a
+    pass takes its own zeroed slice; ONE clear per pass, at its start, so no memset sits between two launches."""
+
+    def __init__(self, n_ints: int, dev):
+        self.t = torch.zeros(max(n_ints, 1), dtype=torch.int32, device=dev)
+        self.off = 0
+
+    def reset(self) -> None:
+        self.t.zero_()
+        self.off = 0
+
+    def take(self, n: int) -> Tensor:
+        if self.off + n > self.t.numel():
+            raise RuntimeError("CUDA srb200: chain flag arena exhausted")
+        v = self.t[self.off:self.off + n]
+        self.off += n
+        return v
+
+
+def _chain_default() -> int:
+    """Convolutions per chained launch in the RRDB trunk (multiple of 5 = whole dense blocks; 0 = one launch per
+    convolution).  SRB_CONV_CHAIN overrides."""
+    v = int(os.environ.get("SRB_CONV_CHAIN", "0"))
+    return max(0, min(v, ops.CHAIN_MAX))
+
+
 class GeneratorEngine:
     def __init__(self, params: Dict[str, torch.nn.Parameter], *, channels: int, filters: int, num_res_blocks: int,
                  num_upsample: int, res_scale: float, impl: int = L.IMPL_TCGEN05):
@@ -48,6 +76,7 @@ class GeneratorEngine:
         self.p = params
         self.ch, self.F, self.nb, self.nup, self.rs = channels, filters, num_res_blocks, num_upsample, float(res_scale)
         self.impl = impl
+        self.chain = _chain_default() if impl == L.IMPL_TCGEN05 else 0
         self._bufs: Dict[Tuple, _Bufs] = {}
         self._pack_key = None
         self._packs_bwd_ready = False
@@ -203,6 +232,9 @@ class GeneratorEngine:
         bf.out = torch.empty(B, self.ch, H, W, device=dev)
         bf.srs = torch.empty(B, self.ch, H, W, device=dev)
         bf.z = torch.empty(B, self.ch, H, W, device=dev)
+        n_flag = 15 * self.nb * ops.chain_flag_ints(B, h, w, 1)
+        bf.flags_f = _FlagArena(n_flag, dev)
+        bf.flags_b = _FlagArena(n_flag if training else 0, dev)
         if training:
             bf.G = [ops.pnhwc_zeros(B, h, w, 5 * F_, dev) for _ in range(3)]
             bf.g_s = ops.pnhwc_zeros(B, h, w, F_, dev)
@@ -232,6 +264,19 @@ class GeneratorEngine:
     def _conv(self, x, x_coff, cin, name, y, y_coff, cout, **kw):
         ops.conv3x3(x, x_coff, cin, self.wp[name], self.bias_packed[name], y, y_coff, cout, impl=self.impl, **kw)
 
+    @staticmethod
+    def _flush(pend: list, arena: _FlagArena, B: int, h: int, w: int) -> None:
+        """Launch the pending convolutions: one chained launch, or a plain one if there is only one."""
+        if not pend:
+            return
+        if len(pend) == 1:
+            a, flops = pend[0]
+            with ops._Prof("conv3x3", flops):
+                L.check(L.lib().srb_conv3x3(C.byref(a), _st()), "conv3x3")
+        else:
+            ops.conv3x3_chain(pend, arena.take(ops.chain_flag_ints(B, h, w, len(pend))))
+        pend.clear()
+
     def forward(self, img: Tensor, *, power: float, multiplier: float, thres: float, training: bool,
                 save_for_backward: bool) -> Tuple[Tensor, Tensor]:
         """models.py:120-135.  ``img`` fp32 [B, channels, h, w] on the GPU.  Returns (out, srs) as fresh tensors."""
@@ -252,7 +297,20 @@ class GeneratorEngine:
                                     self._w("conv1").data_ptr(), self._b("conv1").data_ptr(), F_,
                                     g[0].data_ptr(), 5 * F_, 0, y2.data_ptr() if y2 is not None else None, F_, 0,
                                     _st()), "conv_in_fwd")
-        # RRDB trunk (models.py:124)
+        # RRDB trunk (models.py:124).  With self.chain > 0 the convolutions of `chain // 5` consecutive dense blocks
+        # go into one persistent launch (csrc/conv_chain.cu) instead of one launch each.
+        chain = self.chain if self.chain >= 5 else 0
+        pend: list = []
+        if chain:
+            bf.flags_f.reset()
+
+        def conv(x, x_coff, cin, name, y, y_coff, cout, **kw):
+            if chain:
+                pend.append(ops.conv3x3_args(x, x_coff, cin, self.wp[name], self.bias_packed[name], y, y_coff, cout,
+                                             impl=self.impl, **kw))
+            else:
+                self._conv(x, x_coff, cin, name, y, y_coff, cout, **kw)
+
         d = 0
         for i in range(self.nb):
             first = d
@@ -260,15 +318,18 @@ class GeneratorEngine:
                 cur = g[d % ng]
                 base = f"res_blocks.{i}.dense_blocks.{j}."
                 for k in range(1, 5):
-                    self._conv(cur, 0, k * F_, base + f"b{k}.0", cur, k * F_, F_, act=L.ACT_LRELU, slope=G_SLOPE)
+                    conv(cur, 0, k * F_, base + f"b{k}.0", cur, k * F_, F_, act=L.ACT_LRELU, slope=G_SLOPE)
                 last = (i == self.nb - 1 and j == 2)
                 dst, dst_off = (bf.trunk, 0) if last else (g[(d + 1) % ng], 0)
                 if j < 2:
-                    self._conv(cur, 0, 5 * F_, base + "b5.0", dst, dst_off, F_, alpha=DRB_SCALE, res1=(cur, 0, 1.0))
+                    conv(cur, 0, 5 * F_, base + "b5.0", dst, dst_off, F_, alpha=DRB_SCALE, res1=(cur, 0, 1.0))
                 else:
-                    self._conv(cur, 0, 5 * F_, base + "b5.0", dst, dst_off, F_, alpha=DRB_SCALE * self.rs,
-                               res1=(cur, 0, self.rs), res2=(g[first % ng], 0, 1.0))
+                    conv(cur, 0, 5 * F_, base + "b5.0", dst, dst_off, F_, alpha=DRB_SCALE * self.rs,
+                         res1=(cur, 0, self.rs), res2=(g[first % ng], 0, 1.0))
                 d += 1
+                if chain and len(pend) + 5 > chain:
+                    self._flush(pend, bf.flags_f, B, h, w)
+        self._flush(pend, bf.flags_f, B, h, w)
         if self.nb == 0:
             raise RuntimeError("CUDA srb200: num_res_blocks must be >= 1")
         # conv2 + long skip (models.py:125-126)
@@ -355,7 +416,19 @@ class GeneratorEngine:
         self._wgrad(bf, bf.trunk, F_, bf.g_s, 0, F_, "conv2")
         hook("conv2.weight")
         self._dconv(bf.g_s, F_, self.wd["conv2"], bf.G[2], 0, F_)
-        # RRDB trunk, last to first
+        # RRDB trunk, last to first.  With self.chain > 0 the five input-gradient convolutions of a dense block are one
+        # chained launch (the block's weight gradients need its complete gradient buffer, so chains stop there).
+        chain = self.chain >= 5
+        pend: list = []
+        if chain:
+            bf.flags_b.reset()
+
+        def dconv(x, cin, pack, y, y_coff, cout, **kw):
+            if chain:
+                pend.append(ops.conv3x3_args(x, 0, cin, pack, None, y, y_coff, cout, impl=self.impl, **kw))
+            else:
+                self._dconv(x, cin, pack, y, y_coff, cout, **kw)
+
         for i in range(self.nb - 1, -1, -1):
             for j in (2, 1, 0):
                 G = bf.G[j]
@@ -364,16 +437,17 @@ class GeneratorEngine:
                 s5 = DRB_SCALE * (self.rs if j == 2 else 1.0)
                 sid = self.rs if j == 2 else 1.0
                 for jj in (4, 3, 2, 1):
-                    self._dconv(G, (5 - jj) * F_, self.wd[base + f"slot{jj}"], G, (5 - jj) * F_, F_,
-                                act=L.ACT_LRELU_MASK, slope=G_SLOPE, mask=(gb, jj * F_))
+                    dconv(G, (5 - jj) * F_, self.wd[base + f"slot{jj}"], G, (5 - jj) * F_, F_,
+                          act=L.ACT_LRELU_MASK, slope=G_SLOPE, mask=(gb, jj * F_))
                 if j > 0:
-                    self._dconv(G, 5 * F_, self.wd[base + "slot0"], bf.G[j - 1], 0, F_, res1=(G, 0, sid))
+                    dconv(G, 5 * F_, self.wd[base + "slot0"], bf.G[j - 1], 0, F_, res1=(G, 0, sid))
                 elif i > 0:
-                    self._dconv(G, 5 * F_, self.wd[base + "slot0"], bf.G[2], 0, F_, res1=(G, 0, sid),
-                                res2=(bf.G[2], 0, 1.0))
+                    dconv(G, 5 * F_, self.wd[base + "slot0"], bf.G[2], 0, F_, res1=(G, 0, sid),
+                          res2=(bf.G[2], 0, 1.0))
                 else:
-                    self._dconv(G, 5 * F_, self.wd[base + "slot0"], bf.g_out1, 0, F_, res1=(G, 0, sid),
-                                res2=(bf.G[2], 0, 1.0))
+                    dconv(G, 5 * F_, self.wd[base + "slot0"], bf.g_out1, 0, F_, res1=(G, 0, sid),
+                          res2=(bf.G[2], 0, 1.0))
+                self._flush(pend, bf.flags_b, B, h, w)
                 if self.impl == L.IMPL_TCGEN05:      # the block's five weight gradients in one launch
                     ops.wgrad3x3_group(gb, G, [(0, k * F_, (5 - k) * F_ if k < 5 else 0, F_,
                                                 bf.grads[base + f"b{k}.0.weight"], bf.grads[base + f"b{k}.0.bias"],

@@ -92,12 +92,13 @@ def pack_dgrad(w: Tensor, ci_off: int, n_out: int, out: Tensor, kb_dst: int, kb_
 
 
 # ------------------------------------------------------------------ convolution
-def conv3x3(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Tensor], y: Tensor, y_coff: int, cout: int,
-            *, alpha: float = 1.0, act: int = L.ACT_NONE, slope: float = 0.01,
-            mask: Optional[Tuple[Tensor, int]] = None, res1: Optional[Tuple[Tensor, int, float]] = None,
-            res2: Optional[Tuple[Tensor, int, float]] = None, shuffle: bool = False, impl: int = L.IMPL_TCGEN05,
-            flags: int = 0) -> None:
-    """y[..., y_coff:y_coff+cout] = epilogue(conv3x3(x[..., x_coff:x_coff+cin])); x, y PNHWC bf16 buffers."""
+def conv3x3_args(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Tensor], y: Tensor, y_coff: int, cout: int,
+                 *, alpha: float = 1.0, act: int = L.ACT_NONE, slope: float = 0.01,
+                 mask: Optional[Tuple[Tensor, int]] = None, res1: Optional[Tuple[Tensor, int, float]] = None,
+                 res2: Optional[Tuple[Tensor, int, float]] = None, shuffle: bool = False, impl: int = L.IMPL_TCGEN05,
+                 flags: int = 0):
+    """srb_conv3x3_args for y[..., y_coff:y_coff+cout] = epilogue(conv3x3(x[..., x_coff:x_coff+cin])) and its
+    algorithmic FLOPs; x, y PNHWC bf16 buffers."""
     _require_cuda(x, "conv3x3")
     B, Hp, Wp, Cx = x.shape
     a = L.Conv3x3Args()
@@ -118,8 +119,32 @@ def conv3x3(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Tensor]
     if res2 is not None:
         a.res2, a.res2_cstride, a.res2_coff, a.res2_scale = res2[0].data_ptr(), res2[0].shape[-1], res2[1], res2[2]
     a.impl, a.flags = impl, flags
-    with _Prof("conv3x3", 2.0 * B * a.H * a.W * 9 * cin * cout):
+    return a, 2.0 * B * a.H * a.W * 9 * cin * cout
+
+
+def conv3x3(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Tensor], y: Tensor, y_coff: int, cout: int,
+            **kw) -> None:
+    """One convolution launch (keyword arguments as conv3x3_args)."""
+    a, flops = conv3x3_args(x, x_coff, cin, wp, bias, y, y_coff, cout, **kw)
+    with _Prof("conv3x3", flops):
         L.check(L.lib().srb_conv3x3(C.byref(a), _stream()), "conv3x3")
+
+
+CHAIN_MAX = 16
+
+
+def chain_flag_ints(batch: int, H: int, W: int, n: int) -> int:
+    return int(L.lib().srb_conv3x3_chain_flag_bytes(batch, H, W, n)) // 4
+
+
+def conv3x3_chain(layers, flags: Tensor) -> None:
+    """``layers`` = list of (args, flops) from conv3x3_args, executed in order inside ONE persistent launch
+    (csrc/conv_chain.cu).  ``flags``: int32 device workspace of chain_flag_ints(...) entries, zero on entry."""
+    n = len(layers)
+    arr = (L.Conv3x3Args * n)(*[a for a, _ in layers])
+    with _Prof("conv3x3", sum(f for _, f in layers)):
+        L.check(L.lib().srb_conv3x3_chain(C.cast(arr, C.c_void_p), n, flags.data_ptr(), flags.numel() * 4, _stream()),
+                "conv3x3_chain")
 
 
 def wgrad_workspace_bytes(batch: int, H: int, W: int, cin: int, cout: int) -> int:

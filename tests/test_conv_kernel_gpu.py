@@ -9,7 +9,9 @@ import torch.nn.functional as F
 
 pytestmark = pytest.mark.gpu
 TOL = 6e-3
-KERNELS = {"one_tap": 0x20000, "filter_row": 0x10000}      # srb_conv3x3_args.flags bits 17 / 16 (conv_igemm.cu)
+# srb_conv3x3_args.flags (conv_igemm.cu): bit 16 filter-row kernel, bit 17 one-tap kernel, bit 18 / 19 forbid / force its
+# 512-row tiles (where the geometry fits them; otherwise the 256- or 128-row tiles run)
+KERNELS = {"one_tap": 0x20000 | 0x40000, "one_tap_512": 0x20000 | 0x80000, "filter_row": 0x10000}
 
 
 def _dev():
@@ -105,3 +107,116 @@ def test_conv3x3_pixelshuffle_store_vs_torch(B, H, W, kernel):
     got = ops.from_pnhwc(y)
     assert (got - ref).abs().max().item() <= TOL * ref.abs().max().item()
     assert ops.read_fault() == 0
+
+
+# ------------------------------------------------------------------ chained launches (csrc/conv_chain.cu)
+def _dense_block_layers(ops, L, buf, dst, packs, biases, F_=64, flags=0):
+    """the five convolutions of a DenseResidualBlock (models.py:34-41) over a growth buffer, as conv3x3_args"""
+    layers = []
+    for k in range(1, 5):
+        layers.append(ops.conv3x3_args(buf, 0, k * F_, packs[k - 1], biases[k - 1], buf, k * F_, F_, act=L.ACT_LRELU,
+                                       slope=0.01, flags=flags))
+    layers.append(ops.conv3x3_args(buf, 0, 5 * F_, packs[4], biases[4], dst, 0, F_, alpha=0.2, res1=(buf, 0, 1.0),
+                                   flags=flags))
+    return layers
+
+
+@pytest.mark.parametrize("B,H,W,nblocks", [
+    (3, 20, 20, 1),        # fewer tiles than CTAs, MT = 1
+    (130, 20, 20, 1),      # several tiles per CTA, MT = 2
+    (512, 20, 20, 3),      # bench geometry, one RRDB = 15 layers in one launch
+    (2, 80, 80, 2),        # HR geometry: halo of 82 rows, two TMA boxes per window
+    (5, 13, 17, 3),        # odd sizes
+])
+def test_conv3x3_chain_is_bitwise_the_sequential_launches(B, H, W, nblocks):
+    """One chained launch over `nblocks` dense blocks == the same convolutions launched one by one (same kernels, same
+    accumulation order: bit-exact), and the sequential result matches torch fp32 on bf16-rounded operands."""
+    dev = _dev()
+    from srb200 import _lib as L, ops
+    g = torch.Generator(device="cuda").manual_seed(B + H + 7 * nblocks)
+    F_ = 64
+    x0 = torch.randn(B, F_, H, W, generator=g, device=dev)
+    ws = [[torch.randn(F_, k * F_, 3, 3, generator=g, device=dev) * (1.0 / (9 * k * F_)) ** 0.5 for k in range(1, 6)]
+          for _ in range(nblocks)]
+    bs = [[torch.randn(F_, generator=g, device=dev) * 0.05 for _ in range(5)] for _ in range(nblocks)]
+    packs = [[ops.pack_fwd(w) for w in wl] for wl in ws]
+
+    def run(chained):
+        bufs = [ops.to_pnhwc(x0, 5 * F_) if i == 0 else ops.pnhwc_zeros(B, H, W, 5 * F_, dev) for i in range(nblocks)]
+        out = ops.pnhwc_zeros(B, H, W, F_, dev)
+        layers = []
+        for i in range(nblocks):
+            dst = out if i == nblocks - 1 else bufs[i + 1]
+            layers += _dense_block_layers(ops, L, bufs[i], dst, packs[i], bs[i], flags=0x20000 if not chained else 0)
+        if chained:
+            flags = torch.zeros(ops.chain_flag_ints(B, H, W, len(layers)), dtype=torch.int32, device=dev)
+            ops.conv3x3_chain(layers, flags)
+        else:
+            for a, _ in layers:
+                import ctypes as C
+                L.check(L.lib().srb_conv3x3(C.byref(a), torch.cuda.current_stream().cuda_stream), "conv3x3")
+        torch.cuda.synchronize()
+        return out, bufs
+
+    out_s, bufs_s = run(False)
+    out_c, bufs_c = run(True)
+    assert ops.read_fault() == 0
+    assert torch.equal(out_c, out_s)
+    for a, b in zip(bufs_c, bufs_s):
+        assert torch.equal(a, b)
+    # and the sequential result is the dense block (first block only: later ones compound bf16 rounding)
+    xr = x0.to(torch.bfloat16).float()
+    feats = [xr]
+    for k in range(5):
+        y = F.conv2d(torch.cat(feats, 1), ws[0][k].to(torch.bfloat16).float(), bs[0][k], padding=1)
+        if k < 4:
+            y = F.leaky_relu(y, 0.01).to(torch.bfloat16).float()
+        feats.append(y)
+    ref = feats[5] * 0.2 + xr
+    got = ops.from_pnhwc(bufs_s[1], 0, F_) if nblocks > 1 else ops.from_pnhwc(out_s)
+    assert (got - ref).abs().max().item() <= 1e-2 * ref.abs().max().item()
+
+
+def test_conv3x3_chain_repeated_launches_are_deterministic():
+    """20 back-to-back chained launches (fresh flags each) give the same bits: no stale read across the flag protocol."""
+    dev = _dev()
+    from srb200 import _lib as L, ops
+    g = torch.Generator(device="cuda").manual_seed(3)
+    B, H, W, F_ = 512, 20, 20, 64
+    x0 = torch.randn(B, F_, H, W, generator=g, device=dev)
+    ws = [torch.randn(F_, k * F_, 3, 3, generator=g, device=dev) * (1.0 / (9 * k * F_)) ** 0.5 for k in range(1, 6)]
+    bs = [torch.randn(F_, generator=g, device=dev) * 0.05 for _ in range(5)]
+    packs = [ops.pack_fwd(w) for w in ws]
+    first = None
+    for it in range(20):
+        buf = ops.to_pnhwc(x0, 5 * F_)
+        out = ops.pnhwc_zeros(B, H, W, F_, dev)
+        layers = _dense_block_layers(ops, L, buf, out, packs, bs)
+        flags = torch.zeros(ops.chain_flag_ints(B, H, W, 5), dtype=torch.int32, device=dev)
+        ops.conv3x3_chain(layers, flags)
+        torch.cuda.synchronize()
+        if first is None:
+            first = (out.clone(), buf.clone())
+        else:
+            assert torch.equal(out, first[0]) and torch.equal(buf, first[1]), it
+    assert ops.read_fault() == 0
+
+
+def test_conv3x3_chain_rejects_bad_arguments():
+    dev = _dev()
+    from srb200 import _lib as L, ops
+    B, H, W, F_ = 2, 20, 20, 64
+    buf = ops.pnhwc_zeros(B, H, W, 5 * F_, dev)
+    out = ops.pnhwc_zeros(B, H, W, F_, dev)
+    w = ops.pack_fwd(torch.zeros(F_, F_, 3, 3, device=dev))
+    a = ops.conv3x3_args(buf, 0, F_, w, None, buf, F_, F_)
+    b = ops.conv3x3_args(buf, 0, F_, w, None, out, 0, F_)
+    small = torch.zeros(1, dtype=torch.int32, device=dev)
+    with pytest.raises(RuntimeError, match="flag workspace too small"):
+        ops.conv3x3_chain([a, b], small)
+    up = ops.pnhwc_zeros(B, 2 * H, 2 * W, F_, dev)
+    w4 = ops.pack_fwd(torch.zeros(4 * F_, F_, 3, 3, device=dev), shuffle=True)
+    c = ops.conv3x3_args(buf, 0, F_, w4, None, up, 0, 4 * F_, shuffle=True)
+    flags = torch.zeros(ops.chain_flag_ints(B, H, W, 2), dtype=torch.int32, device=dev)
+    with pytest.raises(RuntimeError, match="share batch"):
+        ops.conv3x3_chain([a, c], flags)

@@ -131,3 +131,38 @@ def test_tcgen05_matches_naive_kernels_bitwise_close():
         b = g(lr.to(dev)).clone()
         g._engine().impl = L.IMPL_TCGEN05
     assert (a - b).abs().max().item() <= 2e-2 * b.abs().max().item()
+
+
+@pytest.mark.parametrize("chain", [5, 15])
+@pytest.mark.parametrize("batch,lr_size,nb", [(130, 20, 2), (6, 13, 1)])
+def test_chained_trunk_is_bitwise_the_per_conv_launches(chain, batch, lr_size, nb):
+    """GeneratorEngine.chain (csrc/conv_chain.cu): dense blocks / RRDBs as single persistent launches give exactly the
+    bits of one launch per convolution - forward (train and eval buffers) and every weight gradient."""
+    dev = _dev()
+    cfg = dict(nb=nb, nup=2, power=1.0, multiplier=1.0, res_scale=0.1, seed=11, gain=1.2, thres=0.0, training=True)
+    g, _ = _build(cfg, dev)
+    _, lr = O.synthetic_jets(batch, lr_size * 4, 4, 5)
+    lr = lr.to(dev)
+    res = {}
+    for c in (0, chain):
+        g._engine().chain = c
+        g.zero_grad(set_to_none=True)
+        g.train()
+        out = g(lr)
+        (out * out).mean().backward()
+        grads = {n: p.grad.clone() for n, p in g.named_parameters() if p.requires_grad}
+        g.eval()
+        with torch.no_grad():
+            ev = g(lr).clone()
+        res[c] = (out.detach().clone(), grads, ev)
+    g._engine().chain = 0
+    from srb200 import ops
+    assert ops.read_fault() == 0
+    assert torch.equal(res[0][0], res[chain][0])
+    assert torch.equal(res[0][2], res[chain][2])
+    for n in res[0][1]:
+        a, b = res[0][1][n], res[chain][1][n]
+        if n.endswith(".bias") or n.startswith(("conv1.", "conv3.2.")):     # summed with fp32 atomics: order varies
+            assert (a - b).abs().max().item() <= 1e-4 * a.abs().max().item() + 1e-12, n
+        else:
+            assert torch.equal(a, b), n
