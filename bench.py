@@ -268,15 +268,25 @@ def run_ours(args):
     conv = agg.get("conv3x3", [0.0, 1e-9, 0])
     wg = agg.get("wgrad3x3", [0.0, 1e-9, 0])
     ach = conv[0] / (conv[1] * 1e-3) / 1e12
-    roofline = {"bound": "tensor", "kernel": "conv3x3_igemm_kernel (tcgen05 implicit GEMM, fwd + dgrad launches)",
+    chain = G._engine().chain
+    kname = ("conv3x3_chain_kernel (tcgen05 implicit GEMM, %d convolutions per persistent launch in the RRDB trunk) + "
+             "conv3x3_igemm_kernel (remaining layers); fwd + dgrad launches" % chain) if chain else \
+        "conv3x3_igemm_kernel (tcgen05 implicit GEMM, fwd + dgrad launches)"
+    roofline = {"bound": "tensor", "kernel": kname,
                 "achieved": ach, "peak": pk["bf16_sustained"], "unit": "TFLOP/s", "frac": ach / pk["bf16_sustained"],
                 "frac_of_burst": ach / pk["bf16_burst"], "peak_source": pk["source"] + ", sustained figure",
-                "traffic": None, "launches_per_step": conv[2], "kernel_ms_per_step": conv[1],
+                "traffic": 623.4e6 if chain == 5 else None,
+                "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum per chained launch (one dense block, "
+                                "B=512) from profiles/r01_s29_ncu_full_conv3x3_chain.txt; bytes" if chain == 5 else None,
+                "launches_per_step": conv[2], "kernel_ms_per_step": conv[1],
                 "share_of_step": conv[1] / ms,
                 "wgrad": {"achieved": wg[0] / (wg[1] * 1e-3) / 1e12, "launches_per_step": wg[2],
                           "kernel_ms_per_step": wg[1], "share_of_step": wg[1] / ms},
-                "how": "algorithmic FLOPs (2*B*H*W*9*Cin*Cout per launch) / CUDA-event time per launch, summed over "
-                       "one instrumented step run right after the timed region"}
+                "ceiling_note": "Cout = 64 makes every MMA 128x64x16: 6 KB of shared-memory operands per 32 tensor "
+                                "clocks = 192 B/clk against 128 B/clk per SM, i.e. 2/3 of the tensor rate at best "
+                                "(48 clk per MMA measured, profiles/r01_s21_mma_rate_probe.txt)",
+                "how": "algorithmic FLOPs (2*B*H*W*9*Cin*Cout per launch, summed over a chained launch) / CUDA-event "
+                       "time per launch, summed over one instrumented step run right after the timed region"}
     train_flops = world * B * (3 * GFLOP_FWD_PER_IMG) * 1e9
     extras = {"tensor_frac_step_vs_sustained": train_flops / (ms * 1e-3) / 1e12 / pk["bf16_sustained"] / world}
 

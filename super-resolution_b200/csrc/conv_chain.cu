@@ -205,6 +205,7 @@ conv3x3_chain_kernel(const __grid_constant__ ChainParams cp) {
       for (int work = blockIdx.x; work < num_work; work += gridDim.x) {
         const int nt = work % n_ntiles;
         const int mt_idx = work / n_ntiles;
+        igemm_prefetch_mask<MT>(p, mt_idx, nt, lg, lane, half);
         mbar_wait(&t_full[as], pt, 6);
         tc_fence_after();
 #pragma unroll 1

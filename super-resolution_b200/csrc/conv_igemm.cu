@@ -68,6 +68,20 @@ __device__ __forceinline__ void load_row64(const __nv_bfloat16* p, uint4 (&v)[8]
 // PixelShuffle-addressed).  Called for valid pixels only.
 // COHERENT = true reads the residual / mask streams with ld.global.cg instead of the non-coherent path: the chained
 // kernel (conv_chain.cu) reads rows that an earlier layer of the SAME launch wrote.
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+// The LeakyReLU' mask rows of a tile do not depend on its accumulators: pull them into L2 before waiting for the MMAs
+// (they are forward activations, long evicted by the time the input-gradient pass reads them).
+template <int MT>
+__device__ __forceinline__ void igemm_prefetch_mask(const IgemmParams& p, int mt_idx, int nt, int lg, int lane, int half) {
+  if (p.act != SRB_ACT_LRELU_MASK) return;
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) {
+    const int q = mt_idx * (128 * MT) + mt * 128 + lg * 32 + lane;
+    if (q < p.R) prefetch_l2(p.mask + static_cast<size_t>(q) * p.mask_cstride + p.mask_coff + nt * 64 + half * 32);
+  }
+}
+
 template <bool COHERENT>
 __device__ __forceinline__ uint4 ld_row16(const uint4* p) { return COHERENT ? __ldcg(p) : __ldg(p); }
 
@@ -299,6 +313,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
       const int nt = work % p.n_ntiles;
       const int mt_idx = work / p.n_ntiles;
+      igemm_prefetch_mask<MT>(p, mt_idx, nt, lg, lane, half);
       mbar_wait(&t_full[as], pt, 6);
       tc_fence_after();
 #pragma unroll 1

@@ -50,6 +50,7 @@ constexpr int kWgMaxGroup = 8;
 constexpr int kWgColsumFloats = 2048;           // widest gradient buffer the bias pass handles (channels)
 struct WgradGroup {
   int n, splits;
+  int dbg;                           // timing experiments (SRB_WGRAD_DBG): 1 = operands loaded for the first ring pass only
   int unit_start[kWgMaxGroup + 1];   // first (cp, cb, dy) unit of every problem
   WgradParams prob[kWgMaxGroup];
 };
@@ -104,6 +105,7 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
       for (int c = 0; c < n_chunks; ++c) {
         const int k0 = (c_begin + c) * kWgKc;
         mbar_wait(&empty[s], ph ^ 1, 11);
+        if ((g.dbg & 1) && c >= kWgStages) { mbar_arrive(&full[s]); if (++s == kWgStages) { s = 0; ph ^= 1; } continue; }
         mbar_expect_tx(&full[s], kWgStageBytes);
         uint8_t* st = smem + s * kWgStageBytes;
         tma_load_2d(st, &tmap_x, p.x_coff + cp * 128, k0, &full[s]);
@@ -308,6 +310,7 @@ int wgrad3x3_tc_launch_group(const srb_wgrad3x3_args* a, int n, cudaStream_t str
   if (make_tmap_2d_bf16(&tg, a0.gy, (uint64_t)a0.gy_cstride, (uint64_t)R, (uint64_t)a0.gy_cstride * 2, 64, kWgGRows)) return 1;
 
   g.n = n; g.splits = splits;
+  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("SRB_WGRAD_DBG"); dbg = e ? atoi(e) : 0; } g.dbg = dbg; }
   float* colsum = (float*)a0.workspace + (need / sizeof(float) - kWgColsumFloats);
   bool any_bias = false;
   ReduceGroup rg{};

@@ -14,6 +14,6 @@ timeout 300 python tools/profile_step.py 512 > gpurun_out/${TAG}_breakdown_b512.
 CMD="python bench.py --steps 1 --warmup 3 --no-extras --no-graph"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 14000 --csv \
     --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launches.log 2>&1
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:${KRE} -s 700 -c 3 \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:${KRE} -s ${SKIP:-100} -c 3 \
     -o gpurun_out/${TAG}_${KRE}_full $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
 echo done
