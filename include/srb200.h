@@ -72,6 +72,10 @@ typedef struct srb_conv3x3_args {
   const void* res2; int res2_cstride, res2_coff; float res2_scale;
   int impl;                    /* SRB_IMPL_* */
   int flags;                   /* bit0: descriptor base-offset mode (bring-up switch) */
+  float* colsum;               /* optional fp32 [64] (cout == 64 only): += sum over valid pixels of the stored outputs,
+                                  per channel, with atomics - the bias gradient of the convolution whose pre-activation
+                                  gradient this launch produces (torch: grad_bias of aten::convolution_backward).  The
+                                  caller zeroes it; srb_wgrad3x3 consumes it through gy_colsum.  tcgen05 kernels only. */
 } srb_conv3x3_args;
 
 int srb_conv3x3(const srb_conv3x3_args* a, void* stream);
@@ -125,6 +129,9 @@ typedef struct srb_wgrad3x3_args {
   void* workspace; size_t workspace_bytes;
   int impl;
   int flags;
+  float* gy_colsum; /* optional fp32 [gy_cstride]: per-channel sums of gy over all pixels, accumulated by the launches
+                       that wrote gy (srb_conv3x3_args.colsum).  When given, the bias gradient is taken from
+                       gy_colsum[gy_coff .. gy_coff+cout) instead of a pass over gy, and those entries are reset to 0. */
 } srb_wgrad3x3_args;
 int srb_wgrad3x3(const srb_wgrad3x3_args* a, void* stream);
 size_t srb_wgrad3x3_workspace_bytes(int batch, int H, int W, int cin, int cout);

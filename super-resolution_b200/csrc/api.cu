@@ -22,7 +22,10 @@ extern "C" int srb_read_fault(unsigned int* fault_out) {
 
 extern "C" int srb_conv3x3(const srb_conv3x3_args* a, void* stream) {
   if (!a || !a->x || !a->w || !a->y) return srb::set_error("conv3x3: null pointer");
-  if (a->impl == SRB_IMPL_NAIVE) return srb::conv3x3_naive_launch(a, (cudaStream_t)stream);
+  if (a->impl == SRB_IMPL_NAIVE) {
+    if (a->colsum) return srb::set_error("conv3x3: colsum is a tcgen05-kernel option");
+    return srb::conv3x3_naive_launch(a, (cudaStream_t)stream);
+  }
   return srb::conv3x3_igemm_launch(a, (cudaStream_t)stream);
 }
 

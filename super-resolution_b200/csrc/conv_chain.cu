@@ -202,6 +202,9 @@ conv3x3_chain_kernel(const __grid_constant__ ChainParams cp) {
       const IgemmParams& p = cp.L[l];
       const bool signal = l + 1 < n_layers;
       int* fl = cp.flags + static_cast<size_t>(l) * n_mtiles;
+      float vs[32];                             // p.colsum: per-column sums over the rows this lane stored
+#pragma unroll
+      for (int i = 0; i < 32; ++i) vs[i] = 0.f;
       for (int work = blockIdx.x; work < num_work; work += gridDim.x) {
         const int nt = work % n_ntiles;
         const int mt_idx = work / n_ntiles;
@@ -231,6 +234,10 @@ conv3x3_chain_kernel(const __grid_constant__ ChainParams cp) {
             }
           }
           if (valid) igemm_store_row<true>(p, v, q, py, px, nt, half);
+          if (p.colsum && valid) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) vs[i] += v[i];
+          }
         }
         tc_fence_before();
         __syncwarp();
@@ -243,6 +250,7 @@ conv3x3_chain_kernel(const __grid_constant__ ChainParams cp) {
         }
         if (++as == 2) { as = 0; pt ^= 1; }
       }
+      if (p.colsum) atomicAdd(p.colsum + half * 32 + lane, warp_colsum32(vs, lane));   // one butterfly per layer
     }
   }
 

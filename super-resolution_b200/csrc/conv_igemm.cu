@@ -53,6 +53,7 @@ struct IgemmParams {
   const __nv_bfloat16* mask; int mask_cstride, mask_coff;
   const __nv_bfloat16* res1; int res1_cstride, res1_coff; float res1_scale;
   const __nv_bfloat16* res2; int res2_cstride, res2_coff; float res2_scale;
+  float* colsum;    // optional [64]: per-channel sums of the stored outputs (bias gradient), n_ntiles == 1 only
   int base_offset_mode;
   int dbg;          // timing experiments only (flags >> 1): 1 no weight reloads, 2 no activation reloads, 4 no epilogue I/O
 };
@@ -80,6 +81,42 @@ __device__ __forceinline__ void igemm_prefetch_mask(const IgemmParams& p, int mt
     const int q = mt_idx * (128 * MT) + mt * 128 + lg * 32 + lane;
     if (q < p.R) prefetch_l2(p.mask + static_cast<size_t>(q) * p.mask_cstride + p.mask_coff + nt * 64 + half * 32);
   }
+}
+
+// Column sums of a warp's 32 rows x 32 columns (v[] = one row per lane): transposing butterfly, 31 shuffles; lane j
+// returns the sum of column j.
+__device__ __forceinline__ float warp_colsum32(const float (&v)[32], int lane) {
+  float a[16];
+  const bool b16 = lane & 16;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const float keep = b16 ? v[i + 16] : v[i], send = b16 ? v[i] : v[i + 16];
+    a[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+  }
+  float b[8];
+  const bool b8 = lane & 8;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float keep = b8 ? a[i + 8] : a[i], send = b8 ? a[i] : a[i + 8];
+    b[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+  }
+  float c[4];
+  const bool b4 = lane & 4;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float keep = b4 ? b[i + 4] : b[i], send = b4 ? b[i] : b[i + 4];
+    c[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+  }
+  float d[2];
+  const bool b2 = lane & 2;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const float keep = b2 ? c[i + 2] : c[i], send = b2 ? c[i] : c[i + 2];
+    d[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+  }
+  const bool b1 = lane & 1;
+  const float keep = b1 ? d[1] : d[0], send = b1 ? d[0] : d[1];
+  return keep + __shfl_xor_sync(0xffffffffu, send, 1);
 }
 
 template <bool COHERENT>
@@ -310,6 +347,9 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
     const int lg = warp & 3;                    // TMEM lane group this warp may access
     const int half = (warp - 5) >> 2;           // which 32 of the 64 columns
     uint32_t as = 0, pt = 0;
+    float vs[32];                               // p.colsum: per-column sums over the rows this lane stored
+#pragma unroll
+    for (int i = 0; i < 32; ++i) vs[i] = 0.f;
     for (int work = blockIdx.x; work < p.num_work; work += gridDim.x) {
       const int nt = work % p.n_ntiles;
       const int mt_idx = work / p.n_ntiles;
@@ -339,6 +379,10 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
           }
         }
         if (valid) igemm_store_row(p, v, q, py, px, nt, half);
+        if (p.colsum && valid) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) vs[i] += v[i];
+        }
       }
       tc_fence_before();
       __syncwarp();
@@ -346,6 +390,7 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
       if (lane == 0) mbar_arrive(&t_empty[as]);
       if (++as == 2) { as = 0; pt ^= 1; }
     }
+    if (p.colsum) atomicAdd(p.colsum + half * 32 + lane, warp_colsum32(vs, lane));   // one butterfly per launch
   }
 
   tc_fence_before();
@@ -457,6 +502,9 @@ int igemm_fill(const srb_conv3x3_args* a, const IgemmPlan& pl, IgemmParams* pp, 
   p.res2 = (const __nv_bfloat16*)a->res2; p.res2_cstride = a->res2_cstride; p.res2_coff = a->res2_coff; p.res2_scale = a->res2_scale;
   p.base_offset_mode = a->flags & 1;
   p.dbg = (a->flags >> 1) & 0x7fff;
+  p.colsum = a->colsum;
+  if (p.colsum && (a->cout != 64 || a->store_mode != SRB_STORE_PLAIN))
+    return set_error("conv3x3: colsum needs cout == 64 and a plain store");
   if (p.act == SRB_ACT_LRELU_MASK && !p.mask) return set_error("conv3x3: mask activation without mask tensor");
   *pp = p;
   return 0;
@@ -465,7 +513,7 @@ int igemm_fill(const srb_conv3x3_args* a, const IgemmPlan& pl, IgemmParams* pp, 
 int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   if (int rc = igemm_check_args(a)) return rc;
   const bool want_row = (a->flags & 0x10000) || (conv_row_enabled() && !(a->flags & 0x20000));
-  if (want_row && ((a->flags >> 1) & 0x7fff) == 0) {      // filter-row kernel (conv_row.cu); -1: geometry does not fit
+  if (want_row && ((a->flags >> 1) & 0x7fff) == 0 && !a->colsum) {      // filter-row kernel (conv_row.cu); -1: geometry does not fit
     const int rc = conv3x3_row_launch(a, stream);
     if (rc >= 0) return rc;
   }

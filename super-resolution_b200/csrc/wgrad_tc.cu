@@ -220,8 +220,8 @@ colsum_kernel(const __nv_bfloat16* __restrict__ g, long long R, int cstride, flo
 // Sum the K splits, scale, and scatter to OIHW.  One thread per (t, ci, co); co fastest so workspace reads coalesce.
 // blockIdx.y selects the problem of the group.  The first `cout` threads of blockIdx.x == 0 also finish the bias
 // gradient from the column sums.
-struct ReduceItem { const float* ws; float* dw; int cin, cin_pad, cout; float alpha; const float* colsum; float* dbias; };
-struct ReduceGroup { int n, splits, accumulate, unshuffle; ReduceItem it[kWgMaxGroup]; };
+struct ReduceItem { const float* ws; float* dw; int cin, cin_pad, cout; float alpha; float* colsum; float* dbias; };
+struct ReduceGroup { int n, splits, accumulate, unshuffle, colsum_clear; ReduceItem it[kWgMaxGroup]; };
 
 __global__ void wgrad_reduce_kernel(const __grid_constant__ ReduceGroup rg) {
   const ReduceItem& r_ = rg.it[blockIdx.y];
@@ -235,6 +235,7 @@ __global__ void wgrad_reduce_kernel(const __grid_constant__ ReduceGroup rg) {
       const int d = rg.unshuffle ? (4 * (co % cq) + co / cq) : co;
       const float v = r_.alpha * r_.colsum[co];
       r_.dbias[d] = rg.accumulate ? r_.dbias[d] + v : v;
+      if (rg.colsum_clear) r_.colsum[co] = 0.f;     // caller-owned sums (srb_wgrad3x3_args.gy_colsum): consumed, reset
     }
   }
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
@@ -311,10 +312,14 @@ int wgrad3x3_tc_launch_group(const srb_wgrad3x3_args* a, int n, cudaStream_t str
 
   g.n = n; g.splits = splits;
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("SRB_WGRAD_DBG"); dbg = e ? atoi(e) : 0; } g.dbg = dbg; }
-  float* colsum = (float*)a0.workspace + (need / sizeof(float) - kWgColsumFloats);
+  for (int i = 0; i < n; ++i)
+    if (a[i].gy_colsum != a0.gy_colsum) return set_error("wgrad3x3 group: problems must share gy_colsum");
+  const bool ext_colsum = a0.gy_colsum != nullptr;
+  float* colsum = ext_colsum ? a0.gy_colsum : (float*)a0.workspace + (need / sizeof(float) - kWgColsumFloats);
   bool any_bias = false;
   ReduceGroup rg{};
   rg.n = n; rg.splits = splits; rg.accumulate = a0.accumulate; rg.unshuffle = a0.unshuffle;
+  rg.colsum_clear = ext_colsum ? 1 : 0;
   long long max_total = 0;
   for (int i = 0; i < n; ++i) {
     const srb_wgrad3x3_args& ai = a[i];
@@ -330,7 +335,7 @@ int wgrad3x3_tc_launch_group(const srb_wgrad3x3_args* a, int n, cudaStream_t str
     const long long tot = 9LL * ai.cin * ai.cout;
     if (tot > max_total) max_total = tot;
   }
-  if (any_bias) {
+  if (any_bias && !ext_colsum) {
     if (a0.gy_cstride > kWgColsumFloats) return set_error("wgrad3x3: gradient buffer too wide for the bias pass");
     cudaMemsetAsync(colsum, 0, sizeof(float) * a0.gy_cstride, stream);
     const int rpb = 256 / (a0.gy_cstride / 8);

@@ -34,7 +34,7 @@ class Conv3x3Args(C.Structure):
         ("mask", C.c_void_p), ("mask_cstride", C.c_int), ("mask_coff", C.c_int),
         ("res1", C.c_void_p), ("res1_cstride", C.c_int), ("res1_coff", C.c_int), ("res1_scale", C.c_float),
         ("res2", C.c_void_p), ("res2_cstride", C.c_int), ("res2_coff", C.c_int), ("res2_scale", C.c_float),
-        ("impl", C.c_int), ("flags", C.c_int),
+        ("impl", C.c_int), ("flags", C.c_int), ("colsum", C.c_void_p),
     ]
 
 
@@ -46,7 +46,7 @@ class Wgrad3x3Args(C.Structure):
         ("dw", C.c_void_p), ("dbias", C.c_void_p), ("alpha", C.c_float),
         ("accumulate", C.c_int), ("unshuffle", C.c_int),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
-        ("impl", C.c_int), ("flags", C.c_int),
+        ("impl", C.c_int), ("flags", C.c_int), ("gy_colsum", C.c_void_p),
     ]
 
 

@@ -238,6 +238,7 @@ class GeneratorEngine:
         bf.flags_b = _FlagArena(n_flag if training else 0, dev)
         if training:
             bf.G = [ops.pnhwc_zeros(B, h, w, 5 * F_, dev) for _ in range(3)]
+            bf.csum = torch.zeros(3, 5 * F_, device=dev)     # per-channel sums of the G buffers (bias gradients)
             bf.g_s = ops.pnhwc_zeros(B, h, w, F_, dev)
             bf.g_out1 = ops.pnhwc_zeros(B, h, w, F_, dev)
             bf.g_hr = ops.pnhwc_zeros(B, H, W, F_, dev)
@@ -416,7 +417,17 @@ class GeneratorEngine:
         # conv2 (+ the long skip: g_s also flows straight into conv1's output, added in conv_in_bwd)
         self._wgrad(bf, bf.trunk, F_, bf.g_s, 0, F_, "conv2")
         hook("conv2.weight")
-        self._dconv(bf.g_s, F_, self.wd["conv2"], bf.G[2], 0, F_)
+        # Bias gradients of the dense blocks: the kernels that write a gradient slot also add up its columns
+        # (srb_conv3x3_args.colsum), so the weight-gradient launch needs no pass over the gradient buffer.
+        fused_bias = self.impl == L.IMPL_TCGEN05 and F_ == 64
+        cs = bf.csum if fused_bias else None
+        if fused_bias:
+            cs.zero_()
+
+        def col(j, slot):
+            return cs[j, slot * F_:(slot + 1) * F_] if fused_bias else None
+
+        self._dconv(bf.g_s, F_, self.wd["conv2"], bf.G[2], 0, F_, colsum=col(2, 0))
         # RRDB trunk, last to first.  With self.chain > 0 the five input-gradient convolutions of a dense block are one
         # chained launch (the block's weight gradients need its complete gradient buffer, so chains stop there).
         chain = self.chain >= 5 and self.impl == L.IMPL_TCGEN05
@@ -439,12 +450,13 @@ class GeneratorEngine:
                 sid = self.rs if j == 2 else 1.0
                 for jj in (4, 3, 2, 1):
                     dconv(G, (5 - jj) * F_, self.wd[base + f"slot{jj}"], G, (5 - jj) * F_, F_,
-                          act=L.ACT_LRELU_MASK, slope=G_SLOPE, mask=(gb, jj * F_))
+                          act=L.ACT_LRELU_MASK, slope=G_SLOPE, mask=(gb, jj * F_), colsum=col(j, 5 - jj))
                 if j > 0:
-                    dconv(G, 5 * F_, self.wd[base + "slot0"], bf.G[j - 1], 0, F_, res1=(G, 0, sid))
+                    dconv(G, 5 * F_, self.wd[base + "slot0"], bf.G[j - 1], 0, F_, res1=(G, 0, sid),
+                          colsum=col(j - 1, 0))
                 elif i > 0:
                     dconv(G, 5 * F_, self.wd[base + "slot0"], bf.G[2], 0, F_, res1=(G, 0, sid),
-                          res2=(bf.G[2], 0, 1.0))
+                          res2=(bf.G[2], 0, 1.0), colsum=col(2, 0))
                 else:
                     dconv(G, 5 * F_, self.wd[base + "slot0"], bf.g_out1, 0, F_, res1=(G, 0, sid),
                           res2=(bf.G[2], 0, 1.0))
@@ -452,7 +464,8 @@ class GeneratorEngine:
                 if self.impl == L.IMPL_TCGEN05:      # the block's five weight gradients in one launch
                     ops.wgrad3x3_group(gb, G, [(0, k * F_, (5 - k) * F_ if k < 5 else 0, F_,
                                                 bf.grads[base + f"b{k}.0.weight"], bf.grads[base + f"b{k}.0.bias"],
-                                                s5 if k == 5 else 1.0) for k in range(1, 6)], bf.ws)
+                                                s5 if k == 5 else 1.0) for k in range(1, 6)], bf.ws,
+                                       gy_colsum=cs[j] if fused_bias else None)
                 else:
                     for k in range(1, 6):
                         self._wgrad(bf, gb, k * F_, G, (5 - k) * F_ if k < 5 else 0, F_, base + f"b{k}.0",

@@ -96,7 +96,7 @@ def conv3x3_args(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Te
                  *, alpha: float = 1.0, act: int = L.ACT_NONE, slope: float = 0.01,
                  mask: Optional[Tuple[Tensor, int]] = None, res1: Optional[Tuple[Tensor, int, float]] = None,
                  res2: Optional[Tuple[Tensor, int, float]] = None, shuffle: bool = False, impl: int = L.IMPL_TCGEN05,
-                 flags: int = 0):
+                 flags: int = 0, colsum: Optional[Tensor] = None):
     """srb_conv3x3_args for y[..., y_coff:y_coff+cout] = epilogue(conv3x3(x[..., x_coff:x_coff+cin])) and its
     algorithmic FLOPs; x, y PNHWC bf16 buffers."""
     _require_cuda(x, "conv3x3")
@@ -119,6 +119,9 @@ def conv3x3_args(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Te
     if res2 is not None:
         a.res2, a.res2_cstride, a.res2_coff, a.res2_scale = res2[0].data_ptr(), res2[0].shape[-1], res2[1], res2[2]
     a.impl, a.flags = impl, flags
+    if colsum is not None:      # fp32 [cout] accumulator of per-channel output sums (bias gradient), cout == 64
+        assert colsum.dtype == torch.float32 and colsum.numel() >= cout and colsum.is_contiguous()
+        a.colsum = colsum.data_ptr()
     return a, 2.0 * B * a.H * a.W * 9 * cin * cout
 
 
@@ -182,9 +185,11 @@ def wgrad_group_workspace_bytes(batch: int, H: int, W: int, cins, couts) -> int:
     return int(L.lib().srb_wgrad3x3_group_workspace_bytes(batch, H, W, n, C.cast(ci, C.c_void_p), C.cast(co, C.c_void_p)))
 
 
-def wgrad3x3_group(x: Tensor, gy: Tensor, problems, workspace: Tensor, *, accumulate: bool = False) -> None:
+def wgrad3x3_group(x: Tensor, gy: Tensor, problems, workspace: Tensor, *, accumulate: bool = False,
+                   gy_colsum: Optional[Tensor] = None) -> None:
     """Several weight gradients over the same buffers in one launch.  ``problems`` = list of
-    (x_coff, cin, gy_coff, cout, dw, dbias_or_None, alpha)."""
+    (x_coff, cin, gy_coff, cout, dw, dbias_or_None, alpha).  ``gy_colsum``: fp32 [channels of gy] column sums of gy
+    accumulated by the convolutions that wrote it (conv3x3_args(colsum=...)); consumed and reset to zero."""
     _require_cuda(x, "wgrad3x3_group")
     B, Hp, Wp, Cx = x.shape
     assert gy.shape[:3] == x.shape[:3]
@@ -199,6 +204,9 @@ def wgrad3x3_group(x: Tensor, gy: Tensor, problems, workspace: Tensor, *, accumu
         a.dw, a.dbias, a.alpha = dw.data_ptr(), _ptr(db), alpha
         a.accumulate, a.unshuffle = int(accumulate), 0
         a.workspace, a.workspace_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+        if gy_colsum is not None:
+            assert gy_colsum.dtype == torch.float32 and gy_colsum.numel() == gy.shape[-1]
+            a.gy_colsum = gy_colsum.data_ptr()
         flops += 2.0 * B * a.H * a.W * 9 * cin * cout
     with _Prof("wgrad3x3", flops):
         L.check(L.lib().srb_wgrad3x3_group(C.cast(arr, C.c_void_p), n, _stream()), "wgrad3x3_group")

@@ -220,3 +220,37 @@ def test_conv3x3_chain_rejects_bad_arguments():
     flags = torch.zeros(ops.chain_flag_ints(B, H, W, 2), dtype=torch.int32, device=dev)
     with pytest.raises(RuntimeError, match="share batch"):
         ops.conv3x3_chain([a, c], flags)
+
+
+@pytest.mark.parametrize("B,H,W,cin", [(3, 20, 20, 64), (130, 20, 20, 128), (512, 20, 20, 64), (2, 80, 80, 64)])
+@pytest.mark.parametrize("chained", [False, True])
+def test_conv3x3_colsum_is_the_bias_gradient(B, H, W, cin, chained):
+    """srb_conv3x3_args.colsum: per-channel sums of the stored outputs over valid pixels (what aten::convolution_backward
+    returns as grad_bias of the consumer), accumulated on top of the caller's values; fp32 sums of the pre-rounding
+    outputs, compared with the sums of the stored bf16 outputs at 2e-3 of the column's absolute mass."""
+    dev = _dev()
+    from srb200 import _lib as L, ops
+    g = torch.Generator(device="cuda").manual_seed(B + cin)
+    xb, _ = _rand_pnhwc(B, H, W, cin, dev, g)
+    mask_b, _ = _rand_pnhwc(B, H, W, 64, dev, g)
+    w = torch.randn(64, cin, 3, 3, generator=g, device=dev) * (2.0 / (9 * cin)) ** 0.5
+    y = ops.pnhwc_zeros(B, H, W, 64, dev)
+    y2 = ops.pnhwc_zeros(B, H, W, 64, dev)
+    cs = torch.full((128,), 1.5, device=dev)
+    wp1, wp2 = ops.pack_fwd(w), ops.pack_fwd(w[:, :64].contiguous())      # the args hold raw pointers: keep these alive
+    a1 = ops.conv3x3_args(xb, 0, cin, wp1, None, y, 0, 64, act=L.ACT_LRELU_MASK, slope=0.01,
+                          mask=(mask_b, 0), colsum=cs[:64])
+    a2 = ops.conv3x3_args(y, 0, 64, wp2, None, y2, 0, 64, alpha=0.5, res1=(y, 0, 1.0), colsum=cs[64:])
+    if chained:
+        ops.conv3x3_chain([a1, a2], torch.zeros(ops.chain_flag_ints(B, H, W, 2), dtype=torch.int32, device=dev))
+    else:
+        import ctypes as C
+        for a, _ in (a1, a2):
+            L.check(L.lib().srb_conv3x3(C.byref(a), torch.cuda.current_stream().cuda_stream), "conv3x3")
+    torch.cuda.synchronize()
+    assert ops.read_fault() == 0
+    for out, got in ((y, cs[:64]), (y2, cs[64:])):
+        o = ops.from_pnhwc(out)
+        ref = o.sum(dim=(0, 2, 3)) + 1.5
+        mass = o.abs().sum(dim=(0, 2, 3)) + 1.0
+        assert ((got - ref).abs() <= 2e-3 * mass).all(), ((got - ref).abs() / mass).max().item()
