@@ -304,6 +304,14 @@ def run_ours(args):
         ms_g = timed(lambda: gts.step(lr, hr), max(3, args.steps), 2, barrier)
         extras["generator_train_images_per_s"] = B / (ms_g * 1e-3)
         extras["generator_train_tensor_frac_vs_sustained"] = B * 3 * GFLOP_FWD_PER_IMG / (ms_g * 1e-3) / 1e3 / pk["bf16_sustained"]
+        # data path: constituent lists -> HR/LR batch on the device, HBM-bound on the image write
+        from srb200 import data as srb_data
+        pairs = O.synthetic_constituents(B, 128, HR, HR, 3).to(dev)
+        ms_dp = timed(lambda: srb_data.extract_batch(pairs, HR, HR, FACTOR), 20, 3, barrier)
+        dp_bytes = B * (128 * 8 + HR * HR * 4 * (1 + 1.0 / FACTOR ** 2))
+        extras["data_path"] = {"images_per_s": B / (ms_dp * 1e-3), "us_per_batch": ms_dp * 1e3,
+                               "achieved_GBps": dp_bytes / (ms_dp * 1e-3) / 1e9, "peak_GBps": pk.get("hbm", None),
+                               "workload": f"extract_batch, {B} lists of 128 (index, energy) pairs -> {HR}x{HR} + pooled"}
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_extras:
         ips, dt = time_cpu(args.cpu_batch, 3, 1)

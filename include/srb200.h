@@ -226,6 +226,15 @@ int srb_gp_fwd(const float* g, int B, int n, float coef, float* norms, float* lo
 int srb_gp_bwd(const float* g, const float* norms, int B, int n, float coef, const float* gloss, float* gg,
                void* stream);
 
+/* ---- data path (csrc/data_path.cu) ---------------------------------------------------
+ * srb_extract_batch: datasets.py:136-145 (extract) + datasets.py:247-249 / models.py:297-305 (SumPool2d) for a batch.
+ *   pairs : fp32 [B][N][2] = (flat index, energy) lists, zero padded (a zero energy ends a list)
+ *   hr    : fp32 [B][1][etaBins][phiBins], hr[b,0,idx % etaBins, idx // etaBins] += energy in list order
+ *   lr    : fp32 [B][1][etaBins/factor][phiBins/factor] = factor x factor sums of hr, or NULL
+ *   n_bad : optional device counter, += entries whose index falls outside the image (the reference raises there) */
+int srb_extract_batch(const float* pairs, int B, int N, int etaBins, int phiBins, int factor, float* hr, float* lr,
+                      int* n_bad, void* stream);
+
 /* Timing experiment aid: clock64 stamps of CTA 0's pipeline when srb_conv3x3 ran with flags bit 4 (tools/exp_conv.py). */
 int srb_igemm_read_stamps(long long* out16);
 

@@ -147,6 +147,46 @@ def sum_pool(x: Tensor, k: int) -> Tensor:
 
 
 # ----------------------------------------------------------------------------
+# data path: constituent lists -> dense images
+# ----------------------------------------------------------------------------
+def extract_numpy(data: np.ndarray, etaBins: int, phiBins: int) -> np.ndarray:
+    """``extract``, datasets.py:136-145: data = [2, N] (row 0 flat index, row 1 energy).  fp32 adds in list order into
+    img[0, idx % etaBins, idx // etaBins]; the loop ends after the first zero-energy entry (which adds nothing)."""
+    img = np.zeros((1, etaBins, phiBins), dtype=np.float32)
+    for i in range(data.shape[1]):
+        pos = float(data[0, i])
+        phi = int(pos // etaBins)
+        eta = int(pos % etaBins)
+        img[0, eta, phi] = np.float32(img[0, eta, phi] + np.float32(data[1, i]))
+        if data[1, i] == 0:
+            break
+    return img
+
+
+def extract_batch(pairs: Tensor, etaBins: int, phiBins: int, factor: int) -> Tuple[Tensor, Tensor]:
+    """A batch of SparseJetDataset.__getitem__ (datasets.py:238-249) without cutter / noise: pairs [B, N, 2] ->
+    (hr [B,1,etaBins,phiBins], lr = SumPool2d(factor)(hr))."""
+    hr = torch.stack([torch.from_numpy(extract_numpy(p.t().numpy(), etaBins, phiBins)) for p in pairs.float()])
+    return hr, sum_pool(hr, factor)
+
+
+def synthetic_constituents(batch: int, n_max: int, etaBins: int, phiBins: int, seed: int, dup_every: int = 3) -> Tensor:
+    """Zero-padded (flat index, energy) lists [batch, n_max, 2]: 5..n_max hits ~ Exp(5); every ``dup_every``-th image
+    repeats some cells (the += of datasets.py:142 matters there) and image 1 uses the whole list (no terminator)."""
+    g = torch.Generator().manual_seed(seed)
+    out = torch.zeros(batch, n_max, 2)
+    for b in range(batch):
+        n = n_max if b == 1 else int(torch.randint(5, n_max, (1,), generator=g))
+        idx = torch.randint(0, etaBins * phiBins, (n,), generator=g).float()
+        if b % dup_every == 0 and n > 8:
+            idx[n // 2:n // 2 + 4] = idx[:4]
+            idx[-1] = idx[0]
+        e = -5.0 * torch.log(1 - torch.rand(n, generator=g)) + 1e-3
+        out[b, :n, 0], out[b, :n, 1] = idx, e
+    return out
+
+
+# ----------------------------------------------------------------------------
 # losses (esrgan.py:457-626), default-active terms only
 # ----------------------------------------------------------------------------
 EPS = 1e-7  # esrgan.py:319
