@@ -263,6 +263,10 @@ conv3x3_chain_kernel(const __grid_constant__ ChainParams cp) {
 }
 
 // ---------------------------------------------------------------------------------- host side
+bool conv_t21_enabled();                                                                       // conv_chain21.cu
+bool conv_t21_plan(const srb_conv3x3_args* a, IgemmPlan* pl);
+int conv3x3_chain21_launch_kernel(const ChainParams& cp, const IgemmPlan& pl, int grid, cudaStream_t stream);
+
 size_t conv3x3_chain_flag_bytes(int batch, int H, int W, int n) {
   // sized for the finer tiling (128 rows) so the caller need not know which one the plan picks
   const long long R = 1LL * batch * (H + 1) * (W + 1);
@@ -277,11 +281,15 @@ int conv3x3_chain_launch(const srb_conv3x3_args* a, int n, int* flags, size_t fl
     if (int rc = igemm_check_args(&a[l])) return rc;
     if (a[l].batch != a[0].batch || a[l].H != a[0].H || a[l].W != a[0].W || a[l].cout != a[0].cout)
       return set_error("conv3x3_chain: all layers must share batch, H, W and cout");
-    if (a[l].store_mode != SRB_STORE_PLAIN) return set_error("conv3x3_chain: plain stores only");
+    if (a[l].store_mode != SRB_STORE_PLAIN && n > 1) return set_error("conv3x3_chain: plain stores only");
     if (a[l].impl != SRB_IMPL_TCGEN05) return set_error("conv3x3_chain: tcgen05 kernels only");
   }
+  // flags bit 20 forces, bit 21 forbids the 2+1-tap kernel (conv_chain21.cu); SRB_CONV_T21=1 makes it the default
   IgemmPlan pl;
-  if (int rc = igemm_make_plan(&a[0], &pl)) return rc;
+  const bool want21 = (a[0].flags & 0x100000) || (conv_t21_enabled() && !(a[0].flags & 0x200000));
+  const bool t21 = want21 && conv_t21_plan(&a[0], &pl);
+  if (!t21)
+    if (int rc = igemm_make_plan(&a[0], &pl)) return rc;
   if (n > 1 && flag_bytes < static_cast<size_t>(n) * pl.n_mtiles * sizeof(int))
     return set_error("conv3x3_chain: flag workspace too small (srb_conv3x3_chain_flag_bytes)");
   if (pl.rows_tile < a[0].W + 2)   // a tile's halo (one image row + 1 pixel) must stay inside its two neighbours
@@ -292,6 +300,7 @@ int conv3x3_chain_launch(const srb_conv3x3_args* a, int n, int* flags, size_t fl
   cp.n_layers = n; cp.n_mtiles = pl.n_mtiles; cp.target = kEpiWarps * cp.L[0].n_ntiles; cp.flags = flags;
   const int sms = sm_count();
   const int grid = cp.L[0].num_work < sms ? cp.L[0].num_work : sms;
+  if (t21) return conv3x3_chain21_launch_kernel(cp, pl, grid, stream);
   cudaError_t e;
   if (pl.MT == 4) {
     static bool attr4 = false;

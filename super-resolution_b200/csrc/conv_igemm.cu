@@ -510,8 +510,17 @@ int igemm_fill(const srb_conv3x3_args* a, const IgemmPlan& pl, IgemmParams* pp, 
   return 0;
 }
 
+bool conv_t21_enabled();                                                                          // conv_chain21.cu
+bool conv_t21_plan(const srb_conv3x3_args* a, struct IgemmPlan* pl);
+int conv3x3_chain_launch(const srb_conv3x3_args* a, int n, int* flags, size_t flag_bytes, cudaStream_t stream);
+
 int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   if (int rc = igemm_check_args(a)) return rc;
+  // 2+1-tap formulation (conv_chain21.cu): a chain of one layer
+  if (((a->flags & 0x100000) || (conv_t21_enabled() && !(a->flags & 0x200000))) && ((a->flags >> 1) & 0x7fff) == 0) {
+    IgemmPlan pl21;
+    if (conv_t21_plan(a, &pl21)) return conv3x3_chain_launch(a, 1, nullptr, 0, stream);    // else: image too wide for it
+  }
   const bool want_row = (a->flags & 0x10000) || (conv_row_enabled() && !(a->flags & 0x20000));
   if (want_row && ((a->flags >> 1) & 0x7fff) == 0 && !a->colsum) {      // filter-row kernel (conv_row.cu); -1: geometry does not fit
     const int rc = conv3x3_row_launch(a, stream);

@@ -78,6 +78,7 @@ class GeneratorEngine:
         self.ch, self.F, self.nb, self.nup, self.rs = channels, filters, num_res_blocks, num_upsample, float(res_scale)
         self.impl = impl
         self.chain = _chain_default() if impl == L.IMPL_TCGEN05 else 0
+        self.conv_flags = 0          # srb_conv3x3_args.flags of every tcgen05 convolution (kernel selection bits, tests)
         self._bufs: Dict[Tuple, _Bufs] = {}
         self._pack_key = None
         self._packs_bwd_ready = False
@@ -264,7 +265,8 @@ class GeneratorEngine:
 
     # ------------------------------------------------------------------ forward
     def _conv(self, x, x_coff, cin, name, y, y_coff, cout, **kw):
-        ops.conv3x3(x, x_coff, cin, self.wp[name], self.bias_packed[name], y, y_coff, cout, impl=self.impl, **kw)
+        ops.conv3x3(x, x_coff, cin, self.wp[name], self.bias_packed[name], y, y_coff, cout, impl=self.impl,
+                    flags=self.conv_flags, **kw)
 
     @staticmethod
     def _flush(pend: list, arena: _FlagArena, B: int, h: int, w: int) -> None:
@@ -309,7 +311,7 @@ class GeneratorEngine:
         def conv(x, x_coff, cin, name, y, y_coff, cout, **kw):
             if chain:
                 pend.append(ops.conv3x3_args(x, x_coff, cin, self.wp[name], self.bias_packed[name], y, y_coff, cout,
-                                             impl=self.impl, **kw))
+                                             impl=self.impl, flags=self.conv_flags, **kw))
             else:
                 self._conv(x, x_coff, cin, name, y, y_coff, cout, **kw)
 
@@ -364,7 +366,7 @@ class GeneratorEngine:
                      unshuffle=unshuffle, workspace=bf.ws, impl=self.impl)
 
     def _dconv(self, x, cin, pack, y, y_coff, cout, **kw):
-        ops.conv3x3(x, 0, cin, pack, None, y, y_coff, cout, impl=self.impl, **kw)
+        ops.conv3x3(x, 0, cin, pack, None, y, y_coff, cout, impl=self.impl, flags=self.conv_flags, **kw)
 
     def backward(self, g_out: Optional[Tensor], g_srs: Optional[Tensor]) -> Dict[str, Tensor]:
         """Gradients of every parameter for the last ``forward(save_for_backward=True)``, given d loss / d out and
@@ -437,7 +439,8 @@ class GeneratorEngine:
 
         def dconv(x, cin, pack, y, y_coff, cout, **kw):
             if chain:
-                pend.append(ops.conv3x3_args(x, 0, cin, pack, None, y, y_coff, cout, impl=self.impl, **kw))
+                pend.append(ops.conv3x3_args(x, 0, cin, pack, None, y, y_coff, cout, impl=self.impl,
+                                             flags=self.conv_flags, **kw))
             else:
                 self._dconv(x, cin, pack, y, y_coff, cout, **kw)
 

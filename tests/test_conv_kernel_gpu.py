@@ -11,7 +11,9 @@ pytestmark = pytest.mark.gpu
 TOL = 6e-3
 # srb_conv3x3_args.flags (conv_igemm.cu): bit 16 filter-row kernel, bit 17 one-tap kernel, bit 18 / 19 forbid / force its
 # 512-row tiles (where the geometry fits them; otherwise the 256- or 128-row tiles run)
-KERNELS = {"one_tap": 0x20000 | 0x40000, "one_tap_512": 0x20000 | 0x80000, "filter_row": 0x10000}
+# bit 20 / 21 force / forbid the 2+1-tap kernel (conv_chain21.cu)
+KERNELS = {"one_tap": 0x20000 | 0x40000 | 0x200000, "one_tap_512": 0x20000 | 0x80000 | 0x200000, "filter_row": 0x10000 | 0x200000,
+           "taps_2_1": 0x100000}
 
 
 def _dev():
@@ -128,7 +130,8 @@ def _dense_block_layers(ops, L, buf, dst, packs, biases, F_=64, flags=0):
     (2, 80, 80, 2),        # HR geometry: halo of 82 rows, two TMA boxes per window
     (5, 13, 17, 3),        # odd sizes
 ])
-def test_conv3x3_chain_is_bitwise_the_sequential_launches(B, H, W, nblocks):
+@pytest.mark.parametrize("kflags", [0, 0x100000], ids=["one_tap", "taps_2_1"])
+def test_conv3x3_chain_is_bitwise_the_sequential_launches(B, H, W, nblocks, kflags):
     """One chained launch over `nblocks` dense blocks == the same convolutions launched one by one (same kernels, same
     accumulation order: bit-exact), and the sequential result matches torch fp32 on bf16-rounded operands."""
     dev = _dev()
@@ -147,7 +150,8 @@ def test_conv3x3_chain_is_bitwise_the_sequential_launches(B, H, W, nblocks):
         layers = []
         for i in range(nblocks):
             dst = out if i == nblocks - 1 else bufs[i + 1]
-            layers += _dense_block_layers(ops, L, bufs[i], dst, packs[i], bs[i], flags=0x20000 if not chained else 0)
+            layers += _dense_block_layers(ops, L, bufs[i], dst, packs[i], bs[i],
+                                          flags=kflags | (0x20000 if not chained else 0))
         if chained:
             flags = torch.zeros(ops.chain_flag_ints(B, H, W, len(layers)), dtype=torch.int32, device=dev)
             ops.conv3x3_chain(layers, flags)

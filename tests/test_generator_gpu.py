@@ -166,3 +166,27 @@ def test_chained_trunk_is_bitwise_the_per_conv_launches(chain, batch, lr_size, n
             assert (a - b).abs().max().item() <= 1e-4 * a.abs().max().item() + 1e-12, n
         else:
             assert torch.equal(a, b), n
+
+
+@pytest.mark.parametrize("batch,lr_size,nup,nb", [(130, 20, 2, 2), (5, 13, 1, 1)])
+def test_taps_2_1_kernel_forward_backward_vs_oracle(batch, lr_size, nup, nb):
+    """the 2+1-tap convolution kernel (csrc/conv_chain21.cu, opt-in) through the whole generator: same tolerances as
+    the default kernels against the fp32 oracle."""
+    dev = _dev()
+    cfg = dict(nb=nb, nup=nup, power=1.0, multiplier=1.0, res_scale=0.1, seed=31, gain=1.2, thres=0.0, training=True)
+    g, sd = _build(cfg, dev)
+    g._engine().conv_flags = 0x100000
+    hr, lr = O.synthetic_jets(batch, lr_size * 2 ** nup, 2 ** nup, 77)
+    out = g(lr.to(dev))
+    (out * out).mean().backward()
+    sdr = {k: (v.clone().requires_grad_(True) if k not in ("power", "multiplier") else v) for k, v in sd.items()}
+    o_ref, _ = O.generator_forward(sdr, lr, res_scale=0.1, thres=0.0, training=True)
+    (o_ref * o_ref).mean().backward()
+    _close(out.detach(), o_ref.detach())
+    for n, p in g.named_parameters():
+        if p.requires_grad:
+            a, b = p.grad.float().cpu().reshape(-1), sdr[n].grad.reshape(-1)
+            cos = torch.dot(a, b).item() / (a.norm().item() * b.norm().item() + 1e-30)
+            assert cos >= GRAD_COS, (n, cos)
+    from srb200 import ops
+    assert ops.read_fault() == 0
