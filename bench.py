@@ -312,6 +312,12 @@ def run_ours(args):
         extras["data_path"] = {"images_per_s": B / (ms_dp * 1e-3), "us_per_batch": ms_dp * 1e3,
                                "achieved_GBps": dp_bytes / (ms_dp * 1e-3) / 1e9, "peak_GBps": pk.get("hbm", None),
                                "workload": f"extract_batch, {B} lists of 128 (index, energy) pairs -> {HR}x{HR} + pooled"}
+        # evaluation statistics: one pass over a batch of HR images, HBM-bound on the read
+        imgs = hr[:B].contiguous()
+        ms_st = timed(lambda: srb_data.image_stats(imgs, 0.05, 4), 20, 3, barrier)
+        extras["eval_stats"] = {"images_per_s": B / (ms_st * 1e-3), "us_per_batch": ms_st * 1e3,
+                                "achieved_GBps": B * HR * HR * 4 / (ms_st * 1e-3) / 1e9, "peak_GBps": pk.get("hbm", None),
+                                "workload": f"image_stats (max, min, mean, nnz, sum, meannnz, 4 hardest) of {B} {HR}x{HR} images"}
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_extras:
         ips, dt = time_cpu(args.cpu_batch, 3, 1)

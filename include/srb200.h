@@ -235,6 +235,13 @@ int srb_gp_bwd(const float* g, const float* norms, int B, int n, float coef, con
 int srb_extract_batch(const float* pairs, int B, int N, int etaBins, int phiBins, int factor, float* hr, float* lr,
                       int* n_bad, void* stream);
 
+/* ---- evaluation post-processing (csrc/eval_stats.cu) ----------------------------------
+ * srb_image_stats: evaluation/eval.py:323-335 (collector modes max, min, mean, nnz, sum, meannnz) and eval.py:98-105
+ * (get_nth_hardest, n = 1..nmax <= 8) for a batch in one pass.
+ *   img : fp32 [B][HW];  out : fp32 [B][6 + nmax] = { max, min, mean, count(> thres), sum, mean of pixels > thres or 0,
+ *   1st .. nmax-th largest pixel (duplicates counted) } */
+int srb_image_stats(const float* img, int B, int HW, float thres, int nmax, float* out, void* stream);
+
 /* Timing experiment aid: clock64 stamps of CTA 0's pipeline when srb_conv3x3 ran with flags bit 4 (tools/exp_conv.py). */
 int srb_igemm_read_stamps(long long* out16);
 

@@ -186,6 +186,23 @@ def synthetic_constituents(batch: int, n_max: int, etaBins: int, phiBins: int, s
     return out
 
 
+def nth_hardest_numpy(arr: np.ndarray, n: int = 1):
+    """``get_nth_hardest``, evaluation/eval.py:98-105: the n-th largest pixel of every image (flattened sort)."""
+    temp = np.squeeze(arr)
+    return [np.sort(temp[i], axis=None)[-n] for i in range(temp.shape[0])]
+
+
+def image_stats_numpy(Ln: np.ndarray, thres: float):
+    """The collector modes of evaluation/eval.py:323-335 on one batch Ln [B,1,H,W]: max, min, mean, nnz, sum
+    (lines 325-333) and meannnz (334-339: mean of the pixels > thres, 0 if there is none)."""
+    meannnz = []
+    for j in range(len(Ln)):
+        nnz = Ln[j][Ln[j] > thres]
+        meannnz.append(0 if len(nnz) == 0 else np.nan_to_num(nnz.mean(), 0))
+    return {"max": Ln.max((1, 2, 3)), "min": Ln.min((1, 2, 3)), "mean": Ln.mean((1, 2, 3)),
+            "nnz": (Ln > thres).sum((1, 2, 3)), "sum": Ln.sum((1, 2, 3)), "meannnz": np.asarray(meannnz)}
+
+
 # ----------------------------------------------------------------------------
 # losses (esrgan.py:457-626), default-active terms only
 # ----------------------------------------------------------------------------

@@ -34,3 +34,23 @@ def extract_batch(pairs: Tensor, etaBins: int, phiBins: int, factor: Optional[in
     if check and int(bad.item()):
         raise IndexError(f"extract_batch: {int(bad.item())} constituent indices outside the {etaBins}x{phiBins} image")
     return hr, lr
+
+
+STAT_NAMES = ("max", "min", "mean", "nnz", "sum", "meannnz")
+
+
+def image_stats(img: Tensor, thres: float = 0.0, nmax: int = 0):
+    """Per-image statistics of a CUDA fp32 batch [B, ...] in one launch: the collector modes of
+    evaluation/eval.py:323-335 plus ``get_nth_hardest`` (eval.py:98-105) for n = 1..nmax.  Returns a dict of [B]
+    tensors keyed by STAT_NAMES and, if nmax > 0, "hardest" = [B, nmax] (column n-1 = n-th hardest constituent)."""
+    if not img.is_cuda:
+        raise RuntimeError("CUDA tensor required for image_stats: super-resolution_b200 has no CPU path")
+    x = img.detach().float().contiguous()
+    B = x.shape[0]
+    out = torch.empty(B, 6 + nmax, device=x.device)
+    L.check(L.lib().srb_image_stats(x.data_ptr(), B, x[0].numel(), float(thres), int(nmax), out.data_ptr(),
+                                    torch.cuda.current_stream().cuda_stream), "image_stats")
+    res = {n: out[:, i] for i, n in enumerate(STAT_NAMES)}
+    if nmax:
+        res["hardest"] = out[:, 6:]
+    return res
