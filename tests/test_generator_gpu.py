@@ -190,3 +190,29 @@ def test_taps_2_1_kernel_forward_backward_vs_oracle(batch, lr_size, nup, nb):
             assert cos >= GRAD_COS, (n, cos)
     from srb200 import ops
     assert ops.read_fault() == 0
+
+
+@pytest.mark.parametrize("filters,batch,lr_size", [(128, 9, 20), (128, 40, 10)])
+def test_generator_width_128_vs_oracle(filters, batch, lr_size):
+    """the width axis of the hyper-parameter sweep (BASELINE configs[4]): filters = 128 runs on the same kernels
+    (two 64-wide output tiles per convolution, chained launches with two n-tiles, column-sum kernel for the biases)."""
+    import models
+    dev = _dev()
+    g = models.GeneratorRRDB(1, filters=filters, num_res_blocks=1, num_upsample=2, res_scale=0.1)
+    sd = O.make_generator_sd(41, filters=filters, num_res_blocks=1, num_upsample=2, gain=1.2)
+    g.load_state_dict(sd, strict=True)
+    g = g.to(dev).train()
+    hr, lr = O.synthetic_jets(batch, lr_size * 4, 4, 78)
+    out = g(lr.to(dev))
+    (out * out).mean().backward()
+    sdr = {k: (v.clone().requires_grad_(True) if k not in ("power", "multiplier") else v) for k, v in sd.items()}
+    o_ref, _ = O.generator_forward(sdr, lr, res_scale=0.1, thres=0.0, training=True)
+    (o_ref * o_ref).mean().backward()
+    _close(out.detach(), o_ref.detach())
+    for n, p in g.named_parameters():
+        if p.requires_grad:
+            a, b = p.grad.float().cpu().reshape(-1), sdr[n].grad.reshape(-1)
+            cos = torch.dot(a, b).item() / (a.norm().item() * b.norm().item() + 1e-30)
+            assert cos >= GRAD_COS, (n, cos)
+    from srb200 import ops
+    assert ops.read_fault() == 0
