@@ -198,7 +198,9 @@ def image_stats_numpy(Ln: np.ndarray, thres: float):
     meannnz = []
     for j in range(len(Ln)):
         nnz = Ln[j][Ln[j] > thres]
-        meannnz.append(0 if len(nnz) == 0 else np.nan_to_num(nnz.mean(), 0))
+        # the reference passes copy=0 positionally (np.nan_to_num(nnz.mean(), 0)), which numpy >= 2 rejects for scalars;
+        # the value is the same: NaN -> 0
+        meannnz.append(0 if len(nnz) == 0 else np.nan_to_num(nnz.mean()))
     return {"max": Ln.max((1, 2, 3)), "min": Ln.min((1, 2, 3)), "mean": Ln.mean((1, 2, 3)),
             "nnz": (Ln > thres).sum((1, 2, 3)), "sum": Ln.sum((1, 2, 3)), "meannnz": np.asarray(meannnz)}
 

@@ -205,10 +205,17 @@ conv3x3_chain_kernel(const __grid_constant__ ChainParams cp) {
       float vs[32];                             // p.colsum: per-column sums over the rows this lane stored
 #pragma unroll
       for (int i = 0; i < 32; ++i) vs[i] = 0.f;
+      // LeakyReLU' mask rows are prefetched into L2 one tile ahead: on the small-K layers the epilogue is the slow side,
+      // so a prefetch issued when the tile's own turn comes has no lead over the loads that need it
+      if (static_cast<int>(blockIdx.x) < num_work)
+        igemm_prefetch_mask<MT>(p, blockIdx.x / n_ntiles, blockIdx.x % n_ntiles, lg, lane, half);
       for (int work = blockIdx.x; work < num_work; work += gridDim.x) {
         const int nt = work % n_ntiles;
         const int mt_idx = work / n_ntiles;
-        igemm_prefetch_mask<MT>(p, mt_idx, nt, lg, lane, half);
+        {
+          const int nw = work + gridDim.x;
+          if (nw < num_work) igemm_prefetch_mask<MT>(p, nw / n_ntiles, nw % n_ntiles, lg, lane, half);
+        }
         mbar_wait(&t_full[as], pt, 6);
         tc_fence_after();
 #pragma unroll 1
