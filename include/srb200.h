@@ -72,6 +72,14 @@ typedef struct srb_conv3x3_args {
   const void* res2; int res2_cstride, res2_coff; float res2_scale;
   int impl;                    /* SRB_IMPL_* */
   int flags;                   /* bit0: descriptor base-offset mode (bring-up switch) */
+  void* sign_out;              /* optional uint32 [pixels][sign_cstride]: word sign_coff + (channel / 32) of a pixel gets
+                                  bit (channel % 32) = (stored output > 0).  Written next to a LeakyReLU output so that
+                                  the input-gradient pass can read LeakyReLU' from 1 bit per element (mask_bits)
+                                  instead of re-reading the bf16 activation. */
+  int sign_cstride, sign_coff;
+  const void* mask_bits;       /* SRB_ACT_LRELU_MASK: if set, the mask comes from these sign words (same layout) and
+                                  `mask` is ignored */
+  int maskb_cstride, maskb_coff;
   float* colsum;               /* optional fp32 [64] (cout == 64 only): += sum over valid pixels of the stored outputs,
                                   per channel, with atomics - the bias gradient of the convolution whose pre-activation
                                   gradient this launch produces (torch: grad_bias of aten::convolution_backward).  The

@@ -23,7 +23,8 @@ extern "C" int srb_read_fault(unsigned int* fault_out) {
 extern "C" int srb_conv3x3(const srb_conv3x3_args* a, void* stream) {
   if (!a || !a->x || !a->w || !a->y) return srb::set_error("conv3x3: null pointer");
   if (a->impl == SRB_IMPL_NAIVE) {
-    if (a->colsum) return srb::set_error("conv3x3: colsum is a tcgen05-kernel option");
+    if (a->colsum || a->sign_out || a->mask_bits)
+      return srb::set_error("conv3x3: colsum / sign_out / mask_bits are tcgen05-kernel options");
     return srb::conv3x3_naive_launch(a, (cudaStream_t)stream);
   }
   return srb::conv3x3_igemm_launch(a, (cudaStream_t)stream);

@@ -176,7 +176,10 @@ conv3x3_chain21_kernel(const __grid_constant__ ChainParams cp) {
 #pragma unroll
           for (int mt = 0; mt < 2; ++mt) {
             const int q = mt_idx * kT21Rows + mt * kT21Sub + m;
-            if (q < p.R) prefetch_l2(p.mask + static_cast<size_t>(q) * p.mask_cstride + p.mask_coff + nt * 64 + half * 32);
+            if (q < p.R) {
+              if (p.mask_bits) prefetch_l2(p.mask_bits + static_cast<size_t>(q) * p.maskb_cstride + p.maskb_coff + nt * 2 + half);
+              else prefetch_l2(p.mask + static_cast<size_t>(q) * p.mask_cstride + p.mask_coff + nt * 64 + half * 32);
+            }
           }
         }
         mbar_wait(&t_full[as], pt, 6);

@@ -53,6 +53,8 @@ struct IgemmParams {
   const __nv_bfloat16* mask; int mask_cstride, mask_coff;
   const __nv_bfloat16* res1; int res1_cstride, res1_coff; float res1_scale;
   const __nv_bfloat16* res2; int res2_cstride, res2_coff; float res2_scale;
+  uint32_t* sign_out; int sign_cstride, sign_coff;          // optional: (output > 0) bits, one word per 32 channels
+  const uint32_t* mask_bits; int maskb_cstride, maskb_coff; // LRELU_MASK from sign words instead of `mask`
   float* colsum;    // optional [64]: per-channel sums of the stored outputs (bias gradient), n_ntiles == 1 only
   int base_offset_mode;
   int dbg;          // timing experiments only (flags >> 1): 1 no weight reloads, 2 no activation reloads, 4 no epilogue I/O
@@ -79,7 +81,9 @@ __device__ __forceinline__ void igemm_prefetch_mask(const IgemmParams& p, int mt
 #pragma unroll
   for (int mt = 0; mt < MT; ++mt) {
     const int q = mt_idx * (128 * MT) + mt * 128 + lg * 32 + lane;
-    if (q < p.R) prefetch_l2(p.mask + static_cast<size_t>(q) * p.mask_cstride + p.mask_coff + nt * 64 + half * 32);
+    if (q >= p.R) continue;
+    if (p.mask_bits) prefetch_l2(p.mask_bits + static_cast<size_t>(q) * p.maskb_cstride + p.maskb_coff + nt * 2 + half);
+    else prefetch_l2(p.mask + static_cast<size_t>(q) * p.mask_cstride + p.mask_coff + nt * 64 + half * 32);
   }
 }
 
@@ -181,6 +185,11 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
   if (p.act == SRB_ACT_LRELU) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.slope;
+  } else if (p.act == SRB_ACT_LRELU_MASK && p.mask_bits) {
+    const uint32_t* wp = p.mask_bits + static_cast<size_t>(q) * p.maskb_cstride + p.maskb_coff + (c0 >> 5);
+    const uint32_t bits = COHERENT ? __ldcg(wp) : __ldg(wp);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] *= ((bits >> i) & 1u) ? 1.f : p.slope;
   } else if (p.act == SRB_ACT_LRELU_MASK) {
     const uint4* mp = reinterpret_cast<const uint4*>(p.mask + static_cast<size_t>(q) * p.mask_cstride +
                                                      p.mask_coff + c0);
@@ -194,6 +203,12 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
         v[8 * i + 2 * j + 1] *= bf16hi(w[j]) > 0.f ? 1.f : p.slope;
       }
     }
+  }
+  if (p.sign_out) {
+    uint32_t bits = 0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) bits |= (v[i] > 0.f ? 1u : 0u) << i;
+    p.sign_out[static_cast<size_t>(q) * p.sign_cstride + p.sign_coff + (c0 >> 5)] = bits;
   }
   uint4* yp = reinterpret_cast<uint4*>(p.y + yrow * p.y_cstride + ycoff + half * 32);
 #pragma unroll
@@ -502,10 +517,14 @@ int igemm_fill(const srb_conv3x3_args* a, const IgemmPlan& pl, IgemmParams* pp, 
   p.res2 = (const __nv_bfloat16*)a->res2; p.res2_cstride = a->res2_cstride; p.res2_coff = a->res2_coff; p.res2_scale = a->res2_scale;
   p.base_offset_mode = a->flags & 1;
   p.dbg = (a->flags >> 1) & 0x7fff;
+  p.sign_out = (uint32_t*)a->sign_out; p.sign_cstride = a->sign_cstride; p.sign_coff = a->sign_coff;
+  p.mask_bits = (const uint32_t*)a->mask_bits; p.maskb_cstride = a->maskb_cstride; p.maskb_coff = a->maskb_coff;
+  if (p.sign_out && a->store_mode != SRB_STORE_PLAIN) return set_error("conv3x3: sign_out needs a plain store");
   p.colsum = a->colsum;
   if (p.colsum && (a->cout != 64 || a->store_mode != SRB_STORE_PLAIN))
     return set_error("conv3x3: colsum needs cout == 64 and a plain store");
-  if (p.act == SRB_ACT_LRELU_MASK && !p.mask) return set_error("conv3x3: mask activation without mask tensor");
+  if (p.act == SRB_ACT_LRELU_MASK && !p.mask && !p.mask_bits)
+    return set_error("conv3x3: mask activation without mask tensor");
   *pp = p;
   return 0;
 }
@@ -522,7 +541,7 @@ int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
     if (conv_t21_plan(a, &pl21)) return conv3x3_chain_launch(a, 1, nullptr, 0, stream);    // else: image too wide for it
   }
   const bool want_row = (a->flags & 0x10000) || (conv_row_enabled() && !(a->flags & 0x20000));
-  if (want_row && ((a->flags >> 1) & 0x7fff) == 0 && !a->colsum) {      // filter-row kernel (conv_row.cu); -1: geometry does not fit
+  if (want_row && ((a->flags >> 1) & 0x7fff) == 0 && !a->colsum && !a->sign_out && !a->mask_bits) {      // filter-row kernel (conv_row.cu); -1: geometry does not fit
     const int rc = conv3x3_row_launch(a, stream);
     if (rc >= 0) return rc;
   }

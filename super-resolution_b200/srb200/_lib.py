@@ -34,7 +34,10 @@ class Conv3x3Args(C.Structure):
         ("mask", C.c_void_p), ("mask_cstride", C.c_int), ("mask_coff", C.c_int),
         ("res1", C.c_void_p), ("res1_cstride", C.c_int), ("res1_coff", C.c_int), ("res1_scale", C.c_float),
         ("res2", C.c_void_p), ("res2_cstride", C.c_int), ("res2_coff", C.c_int), ("res2_scale", C.c_float),
-        ("impl", C.c_int), ("flags", C.c_int), ("colsum", C.c_void_p),
+        ("impl", C.c_int), ("flags", C.c_int),
+        ("sign_out", C.c_void_p), ("sign_cstride", C.c_int), ("sign_coff", C.c_int),
+        ("mask_bits", C.c_void_p), ("maskb_cstride", C.c_int), ("maskb_coff", C.c_int),
+        ("colsum", C.c_void_p),
     ]
 
 

@@ -240,6 +240,10 @@ class GeneratorEngine:
         if training:
             bf.G = [ops.pnhwc_zeros(B, h, w, 5 * F_, dev) for _ in range(3)]
             bf.csum = torch.zeros(3, 5 * F_, device=dev)     # per-channel sums of the G buffers (bias gradients)
+            # LeakyReLU sign bits of slots 1..4 of every dense block (F = 64: two 32-bit words per slot and pixel),
+            # written by the forward convolutions and read by the input-gradient pass instead of the bf16 activations
+            bf.sign = [torch.zeros(B, h + 1, w + 1, 8, dtype=torch.int32, device=dev) for _ in range(3 * self.nb)] \
+                if F_ == 64 else None
             bf.g_s = ops.pnhwc_zeros(B, h, w, F_, dev)
             bf.g_out1 = ops.pnhwc_zeros(B, h, w, F_, dev)
             bf.g_hr = ops.pnhwc_zeros(B, H, W, F_, dev)
@@ -321,8 +325,11 @@ class GeneratorEngine:
             for j in range(3):
                 cur = g[d % ng]
                 base = f"res_blocks.{i}.dense_blocks.{j}."
+                sign = bf.sign[d] if (save_for_backward and self.impl == L.IMPL_TCGEN05 and
+                                      getattr(bf, "sign", None) is not None) else None
                 for k in range(1, 5):
-                    conv(cur, 0, k * F_, base + f"b{k}.0", cur, k * F_, F_, act=L.ACT_LRELU, slope=G_SLOPE)
+                    conv(cur, 0, k * F_, base + f"b{k}.0", cur, k * F_, F_, act=L.ACT_LRELU, slope=G_SLOPE,
+                         sign_out=(sign, 2 * (k - 1)) if sign is not None else None)
                 last = (i == self.nb - 1 and j == 2)
                 dst, dst_off = (bf.trunk, 0) if last else (g[(d + 1) % ng], 0)
                 if j < 2:
@@ -451,9 +458,11 @@ class GeneratorEngine:
                 base = f"res_blocks.{i}.dense_blocks.{j}."
                 s5 = DRB_SCALE * (self.rs if j == 2 else 1.0)
                 sid = self.rs if j == 2 else 1.0
+                sign = bf.sign[3 * i + j] if (self.impl == L.IMPL_TCGEN05 and bf.sign is not None) else None
                 for jj in (4, 3, 2, 1):
+                    mk = dict(mask_bits=(sign, 2 * (jj - 1))) if sign is not None else dict(mask=(gb, jj * F_))
                     dconv(G, (5 - jj) * F_, self.wd[base + f"slot{jj}"], G, (5 - jj) * F_, F_,
-                          act=L.ACT_LRELU_MASK, slope=G_SLOPE, mask=(gb, jj * F_), colsum=col(j, 5 - jj))
+                          act=L.ACT_LRELU_MASK, slope=G_SLOPE, colsum=col(j, 5 - jj), **mk)
                 if j > 0:
                     dconv(G, 5 * F_, self.wd[base + "slot0"], bf.G[j - 1], 0, F_, res1=(G, 0, sid),
                           colsum=col(j - 1, 0))

@@ -96,7 +96,8 @@ def conv3x3_args(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Te
                  *, alpha: float = 1.0, act: int = L.ACT_NONE, slope: float = 0.01,
                  mask: Optional[Tuple[Tensor, int]] = None, res1: Optional[Tuple[Tensor, int, float]] = None,
                  res2: Optional[Tuple[Tensor, int, float]] = None, shuffle: bool = False, impl: int = L.IMPL_TCGEN05,
-                 flags: int = 0, colsum: Optional[Tensor] = None):
+                 flags: int = 0, colsum: Optional[Tensor] = None, sign_out: Optional[Tuple[Tensor, int]] = None,
+                 mask_bits: Optional[Tuple[Tensor, int]] = None):
     """srb_conv3x3_args for y[..., y_coff:y_coff+cout] = epilogue(conv3x3(x[..., x_coff:x_coff+cin])) and its
     algorithmic FLOPs; x, y PNHWC bf16 buffers."""
     _require_cuda(x, "conv3x3")
@@ -119,6 +120,12 @@ def conv3x3_args(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Te
     if res2 is not None:
         a.res2, a.res2_cstride, a.res2_coff, a.res2_scale = res2[0].data_ptr(), res2[0].shape[-1], res2[1], res2[2]
     a.impl, a.flags = impl, flags
+    if sign_out is not None:    # (int32 [B, H+1, W+1, words], first word): (output > 0) bits, 32 channels per word
+        assert sign_out[0].dtype == torch.int32 and sign_out[0].shape[:3] == y.shape[:3]
+        a.sign_out, a.sign_cstride, a.sign_coff = sign_out[0].data_ptr(), sign_out[0].shape[-1], sign_out[1]
+    if mask_bits is not None:   # LeakyReLU' from such sign words instead of the bf16 activation
+        assert mask_bits[0].dtype == torch.int32 and mask_bits[0].shape[:3] == y.shape[:3]
+        a.mask_bits, a.maskb_cstride, a.maskb_coff = mask_bits[0].data_ptr(), mask_bits[0].shape[-1], mask_bits[1]
     if colsum is not None:      # fp32 [cout] accumulator of per-channel output sums (bias gradient), cout == 64
         assert colsum.dtype == torch.float32 and colsum.numel() >= cout and colsum.is_contiguous()
         a.colsum = colsum.data_ptr()

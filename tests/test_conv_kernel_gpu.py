@@ -258,3 +258,31 @@ def test_conv3x3_colsum_is_the_bias_gradient(B, H, W, cin, chained):
         ref = o.sum(dim=(0, 2, 3)) + 1.5
         mass = o.abs().sum(dim=(0, 2, 3)) + 1.0
         assert ((got - ref).abs() <= 2e-3 * mass).all(), ((got - ref).abs() / mass).max().item()
+
+
+@pytest.mark.parametrize("B,H,W", [(3, 20, 20), (130, 20, 20), (2, 80, 80)])
+def test_conv3x3_sign_bits_reproduce_the_activation_mask(B, H, W):
+    """sign_out / mask_bits: a LeakyReLU convolution writes (output > 0) bits; an input-gradient convolution masked by
+    those bits gives exactly the bits of the one masked by the bf16 activation itself."""
+    dev = _dev()
+    from srb200 import _lib as L, ops
+    g = torch.Generator(device="cuda").manual_seed(B + H)
+    xb, _ = _rand_pnhwc(B, H, W, 64, dev, g)
+    gb, _ = _rand_pnhwc(B, H, W, 128, dev, g)
+    w1 = ops.pack_fwd(torch.randn(64, 64, 3, 3, generator=g, device=dev) * 0.06)
+    w2 = ops.pack_fwd(torch.randn(64, 128, 3, 3, generator=g, device=dev) * 0.04)
+    bias = torch.randn(64, generator=g, device=dev) * 0.1
+    act = ops.pnhwc_zeros(B, H, W, 320, dev)
+    sign = torch.zeros(B, H + 1, W + 1, 8, dtype=torch.int32, device=dev)
+    ops.conv3x3(xb, 0, 64, w1, bias, act, 128, 64, act=L.ACT_LRELU, slope=0.01, sign_out=(sign, 2))
+    y_ref, y_bits = ops.pnhwc_zeros(B, H, W, 64, dev), ops.pnhwc_zeros(B, H, W, 64, dev)
+    ops.conv3x3(gb, 0, 128, w2, None, y_ref, 0, 64, act=L.ACT_LRELU_MASK, slope=0.01, mask=(act, 128))
+    ops.conv3x3(gb, 0, 128, w2, None, y_bits, 0, 64, act=L.ACT_LRELU_MASK, slope=0.01, mask_bits=(sign, 2))
+    torch.cuda.synchronize()
+    assert ops.read_fault() == 0
+    assert torch.equal(y_ref, y_bits)
+    a = ops.from_pnhwc(act, 128, 64)
+    words = sign[:, :H, :W, 2:4].reshape(B, H, W, 2, 1)
+    bits = ((words >> torch.arange(32, device=dev, dtype=torch.int32)) & 1).reshape(B, H, W, 64).permute(0, 3, 1, 2)
+    assert torch.equal(bits.bool(), a > 0)
+    assert int(sign[:, :, :, :2].abs().sum()) == 0 and int(sign[:, :, :, 4:].abs().sum()) == 0    # other words untouched
