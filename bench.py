@@ -275,9 +275,9 @@ def run_ours(args):
     roofline = {"bound": "tensor", "kernel": kname,
                 "achieved": ach, "peak": pk["bf16_sustained"], "unit": "TFLOP/s", "frac": ach / pk["bf16_sustained"],
                 "frac_of_burst": ach / pk["bf16_burst"], "peak_source": pk["source"] + ", sustained figure",
-                "traffic": 623.4e6 if chain == 5 else None,
+                "traffic": 450.2e6 if chain == 5 else None,
                 "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum per chained launch (one dense block, "
-                                "B=512) from profiles/r01_s29_ncu_full_conv3x3_chain.txt; bytes" if chain == 5 else None,
+                                "B=512) from profiles/r01_s29b_ncu_full_conv3x3_chain.txt; bytes" if chain == 5 else None,
                 "launches_per_step": conv[2], "kernel_ms_per_step": conv[1],
                 "share_of_step": conv[1] / ms,
                 "wgrad": {"achieved": wg[0] / (wg[1] * 1e-3) / 1e12, "launches_per_step": wg[2],

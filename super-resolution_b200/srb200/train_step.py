@@ -11,6 +11,7 @@ returned as device scalars.  With a process group, gradients (and the gate value
 one contiguous message per optimizer, launched as soon as that optimizer's backward has finished."""
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Sequence
 
 import torch
@@ -39,6 +40,11 @@ class GANTrainStep:
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self._work = {}
+        # The discriminator steps need nothing from the generator's backward pass (only the detached generated images
+        # and the discriminator forward already computed in the generator step), so they can run on a second stream
+        # beside it: bandwidth / latency-bound kernels next to tensor-bound ones.  SRB_OVERLAP_D=0/1.
+        self.overlap_d = os.environ.get("SRB_OVERLAP_D", "0") == "1"
+        self._d_stream = None
         # bucketed gradient all-reduce overlapped with the generator's backward (srb200/dp.py)
         self._g_sync = DP.BucketedAllReduce(self.opt_G.flat_g, process_group) if self.world > 1 else None
         self._g_off = {n: o for (n, _), o in zip(((n, p) for n, p in generator.named_parameters() if p.requires_grad),
@@ -112,6 +118,17 @@ class GANTrainStep:
             g[k].add_(g_adv)
             out_losses[f"adv{k}"] = l_adv.detach()
             loss_G = loss_G + self.lambdas[k] * self.l_adv * l_adv.detach()
+        main = torch.cuda.current_stream()
+        if self.overlap_d:
+            if self._d_stream is None:
+                self._d_stream = torch.cuda.Stream()
+            fork = torch.cuda.Event()
+            fork.record(main)
+            self._d_stream.wait_event(fork)
+            with torch.cuda.stream(self._d_stream):
+                self._discriminator_steps(imgs_hr, generated, epsilons, out_losses, B, dev)
+            join = torch.cuda.Event()
+            join.record(self._d_stream)
         if self._g_sync is not None:
             self._g_sync.reset()
             eng.ready_hook = lambda name: self._g_sync.mark_ready(self._g_off[name])
@@ -125,8 +142,14 @@ class GANTrainStep:
             self._g_sync.finish()
         self.opt_G.step(grad_scale=1.0 / self.world, gathered=True)                        # esrgan.py:555
         out_losses["g_loss"] = loss_G
+        if self.overlap_d:
+            main.wait_event(join)
+        else:
+            self._discriminator_steps(imgs_hr, generated, epsilons, out_losses, B, dev)
+        return out_losses
 
-        # ---------------- discriminators ----------------
+    def _discriminator_steps(self, imgs_hr, generated, epsilons, out_losses, B, dev) -> None:
+        """esrgan.py:561-626 for every active discriminator (on the current stream)."""
         for k in range(2):
             d = self.Ds[k]
             if self.lambdas[k] <= 0 or d is None:
@@ -173,7 +196,6 @@ class GANTrainStep:
                 DP.sync_gate(gate, self.pg)
             opt.step(gate=(gate, self.d_threshold), grad_scale=1.0 / self.world, gathered=True)   # 623-624
             out_losses[f"d_loss{k}"] = loss_D.detach()
-        return out_losses
 
 
 class GraphedStep:
