@@ -123,12 +123,7 @@ class GANTrainStep:
             if self._d_stream is None:
                 self._d_stream = torch.cuda.Stream()
             fork = torch.cuda.Event()
-            fork.record(main)
-            self._d_stream.wait_event(fork)
-            with torch.cuda.stream(self._d_stream):
-                self._discriminator_steps(imgs_hr, generated, epsilons, out_losses, B, dev)
-            join = torch.cuda.Event()
-            join.record(self._d_stream)
+            fork.record(main)          # the discriminator steps depend on the work up to here only
         if self._g_sync is not None:
             self._g_sync.reset()
             eng.ready_hook = lambda name: self._g_sync.mark_ready(self._g_off[name])
@@ -143,6 +138,13 @@ class GANTrainStep:
         self.opt_G.step(grad_scale=1.0 / self.world, gathered=True)                        # esrgan.py:555
         out_losses["g_loss"] = loss_G
         if self.overlap_d:
+            # issued after the generator's backward on the host (FusedAdam.step bumps the global parameter epoch the
+            # generator engine checks), but ordered after `fork` only: inside the CUDA graph they are a parallel branch
+            self._d_stream.wait_event(fork)
+            with torch.cuda.stream(self._d_stream):
+                self._discriminator_steps(imgs_hr, generated, epsilons, out_losses, B, dev)
+            join = torch.cuda.Event()
+            join.record(self._d_stream)
             main.wait_event(join)
         else:
             self._discriminator_steps(imgs_hr, generated, epsilons, out_losses, B, dev)
