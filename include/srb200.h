@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define SRB_ABI_VERSION 1
+#define SRB_ABI_VERSION 2   /* 2: srb_conv3x3_args gained sign_out / mask_bits / colsum, srb_wgrad3x3_args gy_colsum (session 29) */
 
 const char* srb_last_error(void);
 int srb_abi_version(void);

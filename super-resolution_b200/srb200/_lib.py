@@ -179,6 +179,9 @@ def lib():
                     fn = getattr(l, name)
                     fn.restype = res
                     fn.argtypes = args
+                if l.srb_abi_version() != 2:
+                    raise RuntimeError("CUDA extension libsrb200.so is stale (ABI %d, bindings expect 2): rebuild it"
+                                       % l.srb_abi_version())
                 _lib = l
     return _lib
 
