@@ -118,7 +118,8 @@ int srb_pack_conv3x3_dgrad(const float* w_oihw, int cout, int cin, int ci_off, i
 /* Table-driven form of the two packs above: one launch for a whole model.  `items_dev` = device array of
  *   struct { const float* w; void* wp; int cout, cin, ci_off, n_out, flag, kind, kb_dst, kb_total; float scale; int pad; }
  * (kind 0: srb_pack_conv3x3_fwd with flag = shuffle; kind 1: srb_pack_conv3x3_dgrad with flag = unshuffle);
- * `block_prefix_dev[i]` = first 256-thread block of item i, `total_blocks` = sum of ceil(elements_i / 256). */
+ * `block_prefix_dev[i]` = first 256-thread block of item i, `total_blocks` = sum of ceil(pairs_i / 256) with
+ * pairs_i = cout * cin (kind 0) or cout * n_out (kind 1): one thread per channel pair handles its nine taps. */
 int srb_pack_batch(const void* items_dev, const int* block_prefix_dev, int n_items, int total_blocks, void* stream);
 
 /* ---- weight gradient of the same convolution -------------------------------------------------

@@ -50,6 +50,9 @@ struct PackItem {
   float scale; int pad;
 };
 
+// One thread per (output channel, input channel) pair: it reads the pair's nine taps (36 contiguous bytes of the OIHW
+// tensor) and writes one bf16 into each of the nine tap planes, where a warp covers 32 consecutive k (64 contiguous
+// bytes).  The element-per-thread mapping it replaces read the fp32 weights with a 36-byte stride (9x sector traffic).
 __global__ void pack_batch_kernel(const PackItem* __restrict__ items, const int* __restrict__ prefix, int n_items) {
   int lo = 0, hi = n_items - 1;
   while (lo < hi) {                               // last item whose first block <= blockIdx.x
@@ -59,31 +62,34 @@ __global__ void pack_batch_kernel(const PackItem* __restrict__ items, const int*
   const PackItem it = items[lo];
   const long long idx = (blockIdx.x - prefix[lo]) * (long long)blockDim.x + threadIdx.x;
   if (it.kind == 0) {
-    const long long total = 9LL * it.cout * it.cin;
-    if (idx >= total) return;
+    const long long pairs = 1LL * it.cout * it.cin;
+    if (idx >= pairs) return;
     const int k = int(idx % 64);
     long long r = idx / 64;
-    const int n = int(r % it.cout); r /= it.cout;
+    const int n = int(r % it.cout);
+    const int kb = int(r / it.cout);
     const int KB = it.cin / 64;
-    const int kb = int(r % KB);
-    const int t = int(r / KB);
     const int C = it.cout / 4;
     const int co = it.flag ? (4 * (n % C) + n / C) : n;
-    it.wp[idx] = __float2bfloat16(it.scale * it.w[((size_t)co * it.cin + kb * 64 + k) * 9 + t]);
+    const float* src = it.w + ((size_t)co * it.cin + kb * 64 + k) * 9;
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+      it.wp[(((size_t)t * KB + kb) * it.cout + n) * 64 + k] = __float2bfloat16(it.scale * __ldg(src + t));
   } else {
-    const long long total = 9LL * it.cout * it.n_out;
-    if (idx >= total) return;
+    const long long pairs = 1LL * it.cout * it.n_out;
+    if (idx >= pairs) return;
     const int k = int(idx % 64);
     long long r = idx / 64;
-    const int n = int(r % it.n_out); r /= it.n_out;
-    const int KBs = it.cout / 64;
-    const int kb = int(r % KBs);
-    const int t = int(r / KBs);
+    const int n = int(r % it.n_out);
+    const int kb = int(r / it.n_out);
     const int kk = kb * 64 + k;
     const int C = it.cout / 4;
     const int co = it.flag ? (4 * (kk % C) + kk / C) : kk;
-    const float v = it.scale * it.w[((size_t)co * it.cin + it.ci_off + n) * 9 + (8 - t)];
-    it.wp[(((size_t)t * it.kb_total + it.kb_dst + kb) * it.n_out + n) * 64 + k] = __float2bfloat16(v);
+    const float* src = it.w + ((size_t)co * it.cin + it.ci_off + n) * 9;
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+      it.wp[(((size_t)t * it.kb_total + it.kb_dst + kb) * it.n_out + n) * 64 + k] =
+          __float2bfloat16(it.scale * __ldg(src + (8 - t)));
   }
 }
 

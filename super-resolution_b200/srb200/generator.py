@@ -130,8 +130,8 @@ class GeneratorEngine:
         prefix, total = [], 0
         for it in items:
             prefix.append(total)
-            elems = 9 * it.cout * (it.cin if it.kind == 0 else it.n_out)
-            total += (elems + 255) // 256
+            pairs = it.cout * (it.cin if it.kind == 0 else it.n_out)      # one thread per (out, in) channel pair
+            total += (pairs + 255) // 256
         pre = torch.tensor(prefix, dtype=torch.int32, device=dev)
         return dict(raw=raw, prefix=pre, n=n, blocks=total)
 

@@ -216,3 +216,34 @@ def test_generator_width_128_vs_oracle(filters, batch, lr_size):
             assert cos >= GRAD_COS, (n, cos)
     from srb200 import ops
     assert ops.read_fault() == 0
+
+
+def test_batched_weight_pack_is_bitwise_the_single_item_kernels():
+    """srb_pack_batch (one launch per direction, one thread per channel pair) against srb_pack_conv3x3_fwd / _dgrad."""
+    dev = _dev()
+    from srb200 import ops
+    cfg = dict(nb=1, nup=2, power=1.0, multiplier=1.0, res_scale=0.1, seed=3, gain=1.0, thres=0.0, training=True)
+    g, _ = _build(cfg, dev)
+    eng = g._engine()
+    eng._ensure_packs(True)
+    torch.cuda.synchronize()
+    F_ = 64
+    for n in eng.names3x3:
+        ref = ops.pack_fwd(eng._w(n), shuffle=n.startswith("upsampling."))
+        assert torch.equal(eng.wp[n], ref), n
+    for n in ("conv2", "conv3.0"):
+        ref = torch.empty_like(eng.wd[n])
+        ops.pack_dgrad(eng._w(n), 0, F_, ref, 0, 1)
+        assert torch.equal(eng.wd[n], ref), n
+    n = "upsampling.0"
+    ref = torch.empty_like(eng.wd[n])
+    ops.pack_dgrad(eng._w(n), 0, F_, ref, 0, 4, unshuffle=True)
+    assert torch.equal(eng.wd[n], ref), n
+    base = "res_blocks.0.dense_blocks.2."
+    for jj in (0, 3):
+        nsrc = 5 - jj
+        ref = torch.empty_like(eng.wd[base + f"slot{jj}"])
+        for kk in range(5, jj, -1):
+            ops.pack_dgrad(eng._w(base + f"b{kk}.0"), jj * F_, F_, ref, 5 - kk, nsrc,
+                           scale=(0.2 * 0.1) if kk == 5 else 1.0)
+        assert torch.equal(eng.wd[base + f"slot{jj}"], ref), jj
