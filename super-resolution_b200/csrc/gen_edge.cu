@@ -331,7 +331,7 @@ extern "C" int srb_conv_in_bwd(const float* img, int B, int Cimg, int H, int W, 
   cudaMemsetAsync(dw, 0, sizeof(float) * F * Cimg * 9, (cudaStream_t)stream);
   cudaMemsetAsync(db, 0, sizeof(float) * F, (cudaStream_t)stream);
   const long long npix = 1LL * B * H * W;
-  int blocks = 4 * sm_count();
+  int blocks = 16 * sm_count();                 // the per-thread pixel loop is a chain of dependent loads: keep it short
   int ppb = ceil_div(npix, blocks); if (ppb < 64) ppb = 64;
   dim3 grid(ceil_div(npix, ppb), (F + 63) / 64);
   conv_in_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, Cimg, H, W, multiplier, power,

@@ -85,6 +85,7 @@ __global__ void pix_mean_kernel(const float* __restrict__ gen, const float* __re
   float a = 0.f;
   if (p < HW) {
     float s = 0.f;
+#pragma unroll 8                                  // same add order, eight images' loads in flight per thread
     for (int b = 0; b < B; ++b) s += gen[(size_t)b * HW + p] - gt[(size_t)b * HW + p];
     s /= B;
     msign[p] = s > 0.f ? 1.f : (s < 0.f ? -1.f : 0.f);
