@@ -66,3 +66,32 @@ def test_weight_reset_and_uniform_reset_apply():
     assert not torch.equal(before, g.conv2.weight)
     g.apply(models.uniform_reset)
     assert float(g.conv3[0].bias.abs().sum()) == 0.0
+
+
+def test_chain_flag_arena_and_default():
+    """host logic of the chained launches: the flag arena hands out disjoint zeroed slices and refuses to overrun;
+    SRB_CONV_CHAIN parses to a clamped integer (default 5 = one launch per dense block)."""
+    import os
+    import torch
+    from srb200 import generator as G
+    a = G._FlagArena(10, "cpu")
+    x, y = a.take(4), a.take(6)
+    assert x.numel() == 4 and y.numel() == 6 and x.data_ptr() != y.data_ptr()
+    x.fill_(7)
+    with pytest.raises(RuntimeError, match="exhausted"):
+        a.take(1)
+    a.reset()
+    assert int(a.t.abs().sum()) == 0 and a.take(10).numel() == 10
+    old = os.environ.get("SRB_CONV_CHAIN")
+    try:
+        os.environ.pop("SRB_CONV_CHAIN", None)
+        assert G._chain_default() == 5
+        os.environ["SRB_CONV_CHAIN"] = "99"
+        assert G._chain_default() == 16
+        os.environ["SRB_CONV_CHAIN"] = "0"
+        assert G._chain_default() == 0
+    finally:
+        if old is None:
+            os.environ.pop("SRB_CONV_CHAIN", None)
+        else:
+            os.environ["SRB_CONV_CHAIN"] = old
