@@ -95,3 +95,13 @@ def test_chain_flag_arena_and_default():
             os.environ.pop("SRB_CONV_CHAIN", None)
         else:
             os.environ["SRB_CONV_CHAIN"] = old
+
+
+def test_data_path_and_eval_stats_have_no_cpu_fallback():
+    """the widened rows follow the same rule as the hot path: CPU tensors are refused loudly"""
+    from srb200 import data
+    pairs = O.synthetic_constituents(2, 16, 80, 80, 1)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        data.extract_batch(pairs, 80, 80, 4)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        data.image_stats(torch.zeros(2, 1, 80, 80), 0.0, 2)
