@@ -219,8 +219,10 @@ int srb_dpack(const float* flat_params, void* dst_bf16, int n_items, const long 
 
 /* ---- losses and optimizer (csrc/optim_loss.cu) ---------------------------------------------------
  * srb_adam_step   : torch.optim.Adam (esrgan.py:299,305,555,624) over one flat fp32 buffer; `state` = device
- *                   float[2] {step, skip}; the update is skipped unless *gate_value > gate_threshold (the
- *                   d_threshold test of esrgan.py:623 without a host sync); gate_value may be NULL.
+ *                   float[4] {step, skip, lr, reserved}; the update is skipped unless *gate_value > gate_threshold
+ *                   (the d_threshold test of esrgan.py:623 without a host sync); gate_value may be NULL.  lr < 0
+ *                   means "use state[2]": the learning rate then lives on the device, so a captured CUDA graph
+ *                   follows ReduceLROnPlateau (esrgan.py:308-310,666-667) without re-capture.
  * srb_pixel_losses: esrgan.py:471,487,490  L1(batch-mean image) and L1(SumPool(gen), lr) + gradient w.r.t. gen.
  * srb_ragan       : esrgan.py:507-508 (u=fake, v=real) and 578-588 (u=real, v=fake): loss, dL/du, dL/dv.
  * srb_gp_fwd/bwd  : esrgan.py:604-605 gradient-penalty reduction and its gradient.                           */

@@ -12,7 +12,10 @@ namespace srb {
 
 int set_error(const char* msg);                         // returns 1
 int set_cuda_error(const char* what, cudaError_t e);    // returns 1
-int sm_count();
+int sm_count();                                         // SMs of the CURRENT device (cached per device)
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (current device, kernel): the attribute is per device, so a
+// process-wide "done" flag would leave the second GPU of a multi-device process at the 48 KB default.
+void ensure_max_smem(const void* kernel, int bytes);
 
 // 2-D bf16 tensor map: dims {inner, outer}, row stride in bytes, box {box_inner, box_outer}, 128B swizzle,
 // out-of-bounds elements read as zero.  Returns 0 on success.

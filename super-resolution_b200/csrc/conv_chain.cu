@@ -310,16 +310,13 @@ int conv3x3_chain_launch(const srb_conv3x3_args* a, int n, int* flags, size_t fl
   if (t21) return conv3x3_chain21_launch_kernel(cp, pl, grid, stream);
   cudaError_t e;
   if (pl.MT == 4) {
-    static bool attr4 = false;
-    if (!attr4) { cudaFuncSetAttribute(conv3x3_chain_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr4 = true; }
+    ensure_max_smem(reinterpret_cast<const void*>(conv3x3_chain_kernel<4>), 227 * 1024);
     e = launch_pdl(conv3x3_chain_kernel<4>, dim3(grid), dim3(kIgemmThreads), pl.smem, stream, cp);
   } else if (pl.MT == 2) {
-    static bool attr2 = false;
-    if (!attr2) { cudaFuncSetAttribute(conv3x3_chain_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr2 = true; }
+    ensure_max_smem(reinterpret_cast<const void*>(conv3x3_chain_kernel<2>), 227 * 1024);
     e = launch_pdl(conv3x3_chain_kernel<2>, dim3(grid), dim3(kIgemmThreads), pl.smem, stream, cp);
   } else {
-    static bool attr1 = false;
-    if (!attr1) { cudaFuncSetAttribute(conv3x3_chain_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr1 = true; }
+    ensure_max_smem(reinterpret_cast<const void*>(conv3x3_chain_kernel<1>), 227 * 1024);
     e = launch_pdl(conv3x3_chain_kernel<1>, dim3(grid), dim3(kIgemmThreads), pl.smem, stream, cp);
   }
   if (e == cudaSuccess) e = cudaGetLastError();

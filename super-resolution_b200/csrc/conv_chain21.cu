@@ -271,8 +271,7 @@ bool conv_t21_plan(const srb_conv3x3_args* a, IgemmPlan* pl) {
 }
 
 int conv3x3_chain21_launch_kernel(const ChainParams& cp, const IgemmPlan& pl, int grid, cudaStream_t stream) {
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(conv3x3_chain21_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr = true; }
+  ensure_max_smem(reinterpret_cast<const void*>(conv3x3_chain21_kernel), 227 * 1024);
   cudaError_t e = launch_pdl(conv3x3_chain21_kernel, dim3(grid), dim3(kIgemmThreads), pl.smem, stream, cp);
   if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return set_cuda_error("conv3x3_chain21 launch", e);

@@ -468,8 +468,7 @@ int conv3x3_row_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   RowSched sc{};
   sc.n_sub = n_sub; sc.units = units; sc.mt_max = mt_max; sc.n_bslots = n_bslots;
   const int grid = units < sms ? (int)units : sms;
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(conv3x3_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); attr = true; }
+  ensure_max_smem(reinterpret_cast<const void*>(conv3x3_row_kernel), 227 * 1024);
   cudaError_t e = launch_pdl(conv3x3_row_kernel, dim3(grid), dim3(kRowThreads), smem, stream, tx, tw, p, sc);
   if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return set_cuda_error("conv3x3_row launch", e);

@@ -63,11 +63,7 @@ extern "C" int srb_extract_batch(const float* pairs, int B, int N, int etaBins, 
     return set_error("extract_batch: image size must be a multiple of the pooling factor");
   const size_t smem = (static_cast<size_t>((etaBins * phiBins + 1) & ~1)) * 4 + static_cast<size_t>(N) * 8;
   if (smem > 227 * 1024) return set_error("extract_batch: image + list do not fit in shared memory");
-  static size_t attr_set = 0;
-  if (smem > 48 * 1024 && smem > attr_set) {
-    cudaFuncSetAttribute(extract_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    attr_set = 227 * 1024;
-  }
+  if (smem > 48 * 1024) ensure_max_smem(reinterpret_cast<const void*>(extract_batch_kernel), 227 * 1024);
   extract_batch_kernel<<<B, 256, smem, (cudaStream_t)stream>>>(reinterpret_cast<const float2*>(pairs), N, etaBins,
                                                                phiBins, factor, hr, lr, n_bad);
   cudaError_t e = cudaGetLastError();

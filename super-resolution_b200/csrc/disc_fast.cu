@@ -292,8 +292,7 @@ static int wgrad_launch(const float* gy, const float* x, float* dw, float* db, i
   const int tpb = int((n_tiles + blocks - 1) / blocks);
   blocks = (n_tiles + tpb - 1) / tpb;
   auto kern = dconv_wgrad_tile_kernel<TO, S>;
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
+  ensure_max_smem(reinterpret_cast<const void*>(kern), 200 * 1024);
   kern<<<(int)blocks, threads, smem, st>>>(gy, x, dw, db, B, Cin, H, W, Cout, Ho, Wo, TY, lanes, tpb);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : set_cuda_error("dconv_wgrad launch", e);

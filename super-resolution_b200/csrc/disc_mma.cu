@@ -859,8 +859,7 @@ static int dmma_conv_launch_t(DmmaConvP& p, cudaStream_t st) {
     const uint32_t box[4] = {uint32_t(p.cin), uint32_t(TC), uint32_t(TR), uint32_t(IMGS)};
     if (make_tmap_4d_bf16(&tmap, p.in, dims, box)) return 1;
   }
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(dmma_conv_kernel<KS, NT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024); attr = true; }
+  ensure_max_smem(reinterpret_cast<const void*>(dmma_conv_kernel<KS, NT, MODE>), 201 * 1024);
   int per_sm = int((224 * 1024) / (smem + 1024)); if (per_sm < 1) per_sm = 1; if (per_sm > 4) per_sm = 4;
   int grid = sm_count() * per_sm; if (grid > p.n_tiles) grid = p.n_tiles;
   dmma_conv_kernel<KS, NT, MODE><<<grid, kDmmaThreads, smem, st>>>(p, tmap);
@@ -929,8 +928,7 @@ static int dmma_wgrad_launch_t(DmmaWgradP& p, cudaStream_t st) {
     const uint32_t box[4] = {uint32_t(MT * 16), uint32_t(p.Wo), uint32_t(TH), uint32_t(IMGS)};
     if (make_tmap_4d_bf16(&tmap_g, p.gz, dims, box)) return 1;
   }
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(dmma_wgrad_kernel<KS, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024); attr = true; }
+  ensure_max_smem(reinterpret_cast<const void*>(dmma_wgrad_kernel<KS, MT>), 201 * 1024);
   int per_sm = int((224 * 1024) / (smem + 1024)); if (per_sm < 1) per_sm = 1; if (per_sm > 3) per_sm = 3;
   // Every CTA ends with cout*cin*9 atomic adds, so a small layer wants few CTAs:  time(g) ~ tiles/g * t_tile +
   // g * atomics / rate  is least at  g = sqrt(tiles * t_tile * rate / atomics)   (t_tile ~ 1.5 us, rate ~ 250 / ns).
@@ -1077,8 +1075,7 @@ extern "C" int srb_dl1_wgrad(const void* gz_bf16, const float* img, float* dw, f
     const uint32_t box[4] = {16, uint32_t(W), uint32_t(p.TH), 1};
     if (make_tmap_4d_bf16(&tg, gz_bf16, dims, box)) return 1;
     if (make_tmap_3d_f32(&ti, img, W, H, B, p.TCp, p.TH + 2)) return 1;
-    static bool attr = false;
-    if (!attr) { cudaFuncSetAttribute(dl1_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; }
+    ensure_max_smem(reinterpret_cast<const void*>(dl1_wgrad_tc_kernel), 100 * 1024);
     if (smem > 100 * 1024) return set_error("dl1_wgrad: band does not fit in shared memory");
     int per_sm = int((224 * 1024) / (smem + 1024)); if (per_sm < 1) per_sm = 1; if (per_sm > 4) per_sm = 4;
     int grid = sm_count() * per_sm; if (grid > p.n_tiles) grid = p.n_tiles;
@@ -1094,8 +1091,7 @@ extern "C" int srb_dl1_wgrad(const void* gz_bf16, const float* img, float* dw, f
   int grid = B * bands; if (grid > sm_count() * 4) grid = sm_count() * 4;
   cudaStream_t st = (cudaStream_t)stream;
 #define SRB_L1(CC) if (C == CC) { \
-    static bool attr = false; \
-    if (!attr) { cudaFuncSetAttribute(dl1_wgrad_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); attr = true; } \
+    ensure_max_smem(reinterpret_cast<const void*>(dl1_wgrad_kernel<CC>), 96 * 1024); \
     dl1_wgrad_kernel<CC><<<grid, CC * 10, smem, st>>>((const __nv_bfloat16*)gz_bf16, img, dw, db, B, H, W, TH); }
   SRB_L1(16) else SRB_L1(32) else SRB_L1(64) else return set_error("dl1_wgrad: channels must be 16, 32 or 64");
 #undef SRB_L1

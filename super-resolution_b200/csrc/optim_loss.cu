@@ -32,7 +32,9 @@ __device__ __forceinline__ float block_sum(float v) {
 }
 
 // ------------------------------------------------------------------ Adam
-// state[0] = step count (float), advanced only when the update is applied.
+// state[0] = step count (float), advanced only when the update is applied; state[1] = skip flag of this step;
+// state[2] = learning rate, used when the host passes lr < 0 (so a captured CUDA graph follows lr schedules:
+// esrgan.py:308-310,666-667 lower lr_g / lr_d with ReduceLROnPlateau).
 __global__ void adam_tick_kernel(float* state, const float* gate_value, float gate_threshold) {
   const bool skip = gate_value && !(*gate_value > gate_threshold);
   state[1] = skip ? 1.f : 0.f;
@@ -44,6 +46,7 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
                             float grad_scale, const float* __restrict__ state) {
   if (state[1] != 0.f) return;                       // gated off (discriminator already "too good")
   const float step = state[0];
+  if (lr < 0.f) lr = state[2];
   const float bc1 = 1.f - powf(b1, step), bc2 = 1.f - powf(b2, step);
   const float step_size = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2);
   const long long n4 = n >> 2;

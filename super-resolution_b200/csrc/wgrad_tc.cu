@@ -345,9 +345,8 @@ int wgrad3x3_tc_launch_group(const srb_wgrad3x3_args* a, int n, cudaStream_t str
     cudaError_t ce = cudaGetLastError();
     if (ce != cudaSuccess) return set_cuda_error("colsum launch", ce);
   }
-  static bool attr = false;
   const size_t smem = 1024 + size_t(kWgStages) * kWgStageBytes + 256;
-  if (!attr) { cudaFuncSetAttribute(wgrad3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr = true; }
+  ensure_max_smem(reinterpret_cast<const void*>(wgrad3x3_tc_kernel), (int)smem);
   const int grid = g.unit_start[n] * splits;
   cudaError_t e = launch_pdl(wgrad3x3_tc_kernel, dim3(grid), dim3(kWgThreads), smem, stream, tx, tg, g);
   if (e == cudaSuccess) e = cudaGetLastError();

@@ -70,12 +70,13 @@ class _GeneratorFn(torch.autograd.Function):
         out, srs = gen._engine().forward(x, power=gen._host_scalar("power"), multiplier=gen._host_scalar("multiplier"),
                                          thres=float(gen.thres), training=gen.training, save_for_backward=need)
         ctx.n = len(params)
+        ctx.fwd_gen = gen._engine()._fwd_gen if need else None
         return out, srs
 
     @staticmethod
     def backward(ctx, g_out, g_srs):
         gen = ctx.gen
-        grads = gen._engine().backward(g_out, g_srs)
+        grads = gen._engine().backward(g_out, g_srs, fwd_gen=ctx.fwd_gen)
         res = []
         for name, p in gen.named_parameters():
             g = grads.get(name) if p.requires_grad else None
@@ -282,6 +283,10 @@ class SumPool2d(torch.nn.Module):
     def forward(self, x):
         if not self._native:
             raise RuntimeError("CUDA srb200: SumPool2d kernels cover stride == k")
+        if not x.is_cuda and torch.cuda.is_available():
+            # datasets.py:160-166,247 pool single CPU images inside Dataset.__getitem__: run the kernel on the device
+            # and hand the result back on the caller's device (still no CPU arithmetic path)
+            return _small.sum_pool(x.cuda(), self.k).to(x.device)
         return _small.sum_pool(x, self.k)
 
 

@@ -83,6 +83,8 @@ class GeneratorEngine:
         self._pack_key = None
         self._packs_bwd_ready = False
         self._saved = None
+        self._fwd_gen = 0            # forward(save_for_backward=True) counter: backward must match the LAST such forward
+        self._bias_perm = {}
         self.grad_views = None       # optional name -> fp32 view: where backward writes parameter gradients
         self.ready_hook = None       # optional callable(param_name): gradients of this and all later parameters are final
         self.names3x3 = self._conv_names()
@@ -170,8 +172,11 @@ class GeneratorEngine:
             b = self._b(n).detach()
             if n.startswith("upsampling."):
                 cout = b.numel()
-                idx = torch.arange(cout, device=dev)
-                b = b[4 * (idx % (cout // 4)) + idx // (cout // 4)].contiguous()
+                idx = self._bias_perm.get((n, str(dev)))
+                if idx is None:                    # built once: the re-pack after every optimizer step is one gather
+                    i = torch.arange(cout, device=dev)
+                    idx = self._bias_perm[(n, str(dev))] = 4 * (i % (cout // 4)) + i // (cout // 4)
+                b = b[idx]
             self.bias_packed[n] = b.float().contiguous()
 
     def _build_bwd_packs(self) -> None:
@@ -216,11 +221,14 @@ class GeneratorEngine:
     # ------------------------------------------------------------------ buffers
     def _get_bufs(self, B: int, h: int, w: int, training: bool, dev) -> _Bufs:
         key = (B, h, w, training, str(dev))
-        bf = self._bufs.get(key)
+        bf = self._bufs.pop(key, None)
         if bf is not None:
+            self._bufs[key] = bf            # re-insert: dict order = recency
             return bf
-        if len(self._bufs) > 4:
-            self._bufs.clear()
+        if len(self._bufs) >= 6:
+            # evict the least recently used shape only (a hyper-parameter sweep or a partial last batch must not drop
+            # the steady-state buffers and force a re-allocation of GBs)
+            del self._bufs[next(iter(self._bufs))]
         F_ = self.F
         bf = _Bufs()
         n_growth = 3 * self.nb if training else 4
@@ -363,8 +371,9 @@ class GeneratorEngine:
                                      int(training), out.data_ptr(), srs.data_ptr(), bf.z.data_ptr(), _st()),
                 "conv_out_fwd")
         if save_for_backward:
+            self._fwd_gen += 1
             self._saved = dict(img=img, bf=bf, power=float(power), multiplier=float(multiplier), thres=float(thres),
-                               training=bool(training), key=self._pack_key)
+                               training=bool(training), key=self._pack_key, gen=self._fwd_gen)
         return out, srs
 
     # ------------------------------------------------------------------ backward
@@ -375,13 +384,19 @@ class GeneratorEngine:
     def _dconv(self, x, cin, pack, y, y_coff, cout, **kw):
         ops.conv3x3(x, 0, cin, pack, None, y, y_coff, cout, impl=self.impl, flags=self.conv_flags, **kw)
 
-    def backward(self, g_out: Optional[Tensor], g_srs: Optional[Tensor]) -> Dict[str, Tensor]:
+    def backward(self, g_out: Optional[Tensor], g_srs: Optional[Tensor], fwd_gen: Optional[int] = None
+                 ) -> Dict[str, Tensor]:
         """Gradients of every parameter for the last ``forward(save_for_backward=True)``, given d loss / d out and
         d loss / d srs (fp32 [B, ch, H, W] or None).  Returns name -> fp32 tensor views of one flat buffer (valid
-        until the next backward of the same shape)."""
+        until the next backward of the same shape).  ``fwd_gen``: the forward this backward belongs to (autograd
+        passes it); the activation buffers hold ONE forward, so a backward for an older one is refused."""
         sv = self._saved
         if sv is None:
             raise RuntimeError("CUDA srb200: backward called without a saved forward")
+        if fwd_gen is not None and fwd_gen != sv["gen"]:
+            raise RuntimeError("CUDA srb200: GeneratorRRDB keeps the activations of its most recent grad-enabled "
+                               "forward only; backward was asked for an earlier forward (two forwards before one "
+                               "backward). Run forward/backward pairs one after the other, as esrgan.py:468,553 does")
         if sv["key"] != self._params_key():
             raise RuntimeError("CUDA srb200: parameters changed between forward and backward")
         bf, img = sv["bf"], sv["img"]

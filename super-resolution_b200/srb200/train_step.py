@@ -207,24 +207,36 @@ class GraphedStep:
     The interpolation draws of the gradient penalty (esrgan.py:598) come from the CUDA generator, whose Philox
     offset torch advances per replay.  NCCL all-reduces issued inside the step are captured with it."""
 
-    def __init__(self, trainer, imgs_lr: torch.Tensor, imgs_hr: torch.Tensor, warmup: int = 3):
+    def __init__(self, trainer, imgs_lr: torch.Tensor, imgs_hr: torch.Tensor, warmup: int = 3, epsilons=None):
+        """``epsilons``: optional per-discriminator (B,1,1,1) device tensors - the graph then reads the interpolation
+        draws of esrgan.py:598 from static buffers that step(..., epsilons=...) refills (reproducible tests)."""
         self.tr = trainer
         self.lr = imgs_lr.detach().clone()
         self.hr = imgs_hr.detach().clone()
+        self.eps = [e.detach().clone() for e in epsilons] if epsilons is not None else None
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             for _ in range(max(warmup, 1)):          # allocates every cached buffer, sets kernel attributes
-                trainer.step(self.lr, self.hr)
+                trainer.step(self.lr, self.hr, epsilons=self.eps)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
-            self.losses = trainer.step(self.lr, self.hr)
+            self.losses = trainer.step(self.lr, self.hr, epsilons=self.eps)
 
-    def step(self, imgs_lr: torch.Tensor, imgs_hr: torch.Tensor):
+    def step(self, imgs_lr: torch.Tensor, imgs_hr: torch.Tensor, epsilons=None):
+        if imgs_lr.shape != self.lr.shape or imgs_hr.shape != self.hr.shape:
+            # the reference's DataLoader has no drop_last (esrgan.py:311-317): the last batch of an epoch is partial.
+            # The graph is shape-specific, so such a batch takes the eager path (same kernels, same optimizers).
+            return self.tr.step(imgs_lr, imgs_hr, epsilons=epsilons)
         self.lr.copy_(imgs_lr, non_blocking=True)
         self.hr.copy_(imgs_hr, non_blocking=True)
+        if self.eps is not None and epsilons is not None:
+            for dst, src in zip(self.eps, epsilons):
+                dst.copy_(src, non_blocking=True)
+        for opt in [self.tr.opt_G] + [o for o in self.tr.opt_D if o is not None]:
+            opt.sync_lr()                        # ReduceLROnPlateau may have moved it since the last replay
         self.graph.replay()
         return self.losses
 

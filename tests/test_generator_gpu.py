@@ -247,3 +247,22 @@ def test_batched_weight_pack_is_bitwise_the_single_item_kernels():
             ops.pack_dgrad(eng._w(base + f"b{kk}.0"), jj * F_, F_, ref, 5 - kk, nsrc,
                            scale=(0.2 * 0.1) if kk == 5 else 1.0)
         assert torch.equal(eng.wd[base + f"slot{jj}"], ref), jj
+
+
+def test_two_forwards_before_one_backward_are_refused():
+    """the engine keeps the activations of ONE grad-enabled forward (esrgan.py's pattern: forward 468, backward 553);
+    a backward that belongs to an older forward must fail loudly instead of using the newer activations."""
+    dev = _dev()
+    cfg = dict(nb=1, nup=1, power=1.0, multiplier=1.0, res_scale=0.1, seed=5, gain=1.0, thres=0.0, training=True)
+    g, _ = _build(cfg, dev)
+    _, lr = O.synthetic_jets(4, 40, 2, 9)
+    a = g(lr[:2].to(dev))
+    b = g(lr[2:].to(dev))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        (a.sum() + b.sum()).backward()
+    g.zero_grad(set_to_none=True)
+    c = g(lr[:2].to(dev))          # a forward under no_grad in between (validation, eval.py:475) does not disturb it
+    with torch.no_grad():
+        g(lr[2:].to(dev))
+    c.sum().backward()
+    assert g.conv2.weight.grad is not None

@@ -43,9 +43,47 @@ def test_fused_adam_matches_torch_and_gate():
     before = [p.detach().clone() for p in ps]
     opt.step(gate=(torch.tensor(0.0005, device=dev), 0.001))
     assert all(torch.equal(a, p.detach()) for a, p in zip(before, ps))
-    assert opt.state[0].item() == 4.0
+    assert opt.dev_state[0].item() == 4.0
     opt.step(gate=(torch.tensor(0.5, device=dev), 0.001))
-    assert opt.state[0].item() == 5.0 and not torch.equal(before[0], ps[0].detach())
+    assert opt.dev_state[0].item() == 5.0 and not torch.equal(before[0], ps[0].detach())
+
+
+def test_fused_adam_lr_lives_on_the_device_and_schedulers_wrap_it():
+    """esrgan.py:308-310,666-667: ReduceLROnPlateau lowers the learning rate of optimizer_G / optimizer_D.  FusedAdam is
+    a torch Optimizer (the scheduler wraps it) and reads lr from device state, so a CUDA graph captured around step()
+    follows the schedule."""
+    dev = _dev()
+    from srb200.optim import FusedAdam
+    g = torch.Generator().manual_seed(5)
+    w0 = torch.randn(257, generator=g)
+    grads = [torch.randn(257, generator=g) for _ in range(6)]
+    p = torch.nn.Parameter(w0.clone().to(dev))
+    r = torch.nn.Parameter(w0.clone())
+    opt = FusedAdam([p], lr=1e-2)
+    ropt = torch.optim.Adam([r], lr=1e-2)
+    sched = torch.optim.lr_scheduler.ReduceLROnPlateau(opt, patience=0, factor=0.1)
+    rsched = torch.optim.lr_scheduler.ReduceLROnPlateau(ropt, patience=0, factor=0.1)
+    static_g = torch.zeros(257, device=dev)
+    p.grad = static_g
+    opt.step()                                   # warm-up outside the capture (also the first reference step)
+    r.grad = torch.zeros(257); ropt.step()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        opt.step()
+    for i, gr in enumerate(grads):
+        if i == 3:                               # two non-improving metrics -> lr drops by 10x on both
+            for s_ in (sched, rsched):
+                s_.step(1.0); s_.step(2.0)
+            assert opt.param_groups[0]["lr"] == pytest.approx(1e-3)
+        static_g.copy_(gr.to(dev))
+        opt.sync_lr()
+        graph.replay()
+        r.grad = gr.clone(); ropt.step()
+    torch.testing.assert_close(p.detach().cpu(), r.detach(), rtol=2e-5, atol=1e-6)
+    sd = opt.state_dict()
+    opt2 = FusedAdam([torch.nn.Parameter(w0.clone().to(dev))], lr=5.0)
+    opt2.load_state_dict(sd)
+    assert opt2.param_groups[0]["lr"] == pytest.approx(1e-3) and opt2.dev_state[2].item() == pytest.approx(1e-3)
 
 
 def test_loss_kernels_match_oracle():
