@@ -30,7 +30,9 @@
 extern "C" {
 #endif
 
-#define SRB_ABI_VERSION 2   /* 2: srb_conv3x3_args gained sign_out / mask_bits / colsum, srb_wgrad3x3_args gy_colsum (session 29) */
+#define SRB_ABI_VERSION 3   /* 2: srb_conv3x3_args gained sign_out / mask_bits / colsum, srb_wgrad3x3_args gy_colsum (session 29)
+                               3: srb_conv3x3_args gained res_f32 / y32 / res3 / chan_scale (round 2: fp32 residual stream of the RRDB
+                                  trunk, num_final_layer_res skip, Dropout2d); srb_adam_step state is float[4] with the device-side lr */
 
 const char* srb_last_error(void);
 int srb_abi_version(void);
@@ -43,7 +45,7 @@ int srb_read_fault(unsigned int* fault_out);
  * LeakyReLU + PixelShuffle (models.py:87-89); conv3.0 + LeakyReLU (models.py:97-98); and, with the
  * "dgrad" weight pack, the input-gradient of all of those (aten::convolution_backward).
  *
- *   v = (acc + bias) * alpha + res1 * res1_scale + res2 * res2_scale
+ *   v = (acc + bias) * chan_scale[image][n] * alpha + res1 * res1_scale + res2 * res2_scale + res3 * res3_scale
  *   act == SRB_ACT_LRELU      : v = v > 0 ? v : slope * v
  *   act == SRB_ACT_LRELU_MASK : v = v * (mask > 0 ? 1 : slope)          (LeakyReLU backward)
  *   store_mode == SRB_STORE_PLAIN  : y[pixel][y_coff + n]
@@ -84,6 +86,17 @@ typedef struct srb_conv3x3_args {
                                   per channel, with atomics - the bias gradient of the convolution whose pre-activation
                                   gradient this launch produces (torch: grad_bias of aten::convolution_backward).  The
                                   caller zeroes it; srb_wgrad3x3 consumes it through gy_colsum.  tcgen05 kernels only. */
+  int res_f32;                 /* bit 0: res1 points at fp32 (strides / offsets in floats), bit 1: the same for res2.  The
+                                  RRDB trunk keeps its residual stream x_{d+1} = x_d + 0.2 conv5(..) (models.py:41,53) in
+                                  fp32 next to the bf16 copy the next convolution reads: 3 nb bf16 roundings of the stream
+                                  are what pushes nb = 23 past the 2e-2 rel-L2 budget. */
+  float* y32;                  /* optional fp32 copy of the stored output (plain store only): y32[pixel][y32_coff + n] */
+  int y32_cstride, y32_coff;
+  const void* res3; int res3_cstride, res3_coff; float res3_scale;   /* third bf16 residual: `out3 + out` of
+                                  num_final_layer_res (models.py:128-130) and its gradient */
+  const float* chan_scale;     /* optional fp32 [batch][cout]: per image and output channel factor on (acc + bias) - the
+                                  Dropout2d mask (0 or 1/(1-p)) on out5 of a DenseResidualBlock (models.py:39-40).  Plain
+                                  store only. */
 } srb_conv3x3_args;
 
 int srb_conv3x3(const srb_conv3x3_args* a, void* stream);
@@ -256,7 +269,11 @@ int srb_image_stats(const float* img, int B, int HW, float thres, int nmax, floa
 /* Timing experiment aid: clock64 stamps of CTA 0's pipeline when srb_conv3x3 ran with flags bit 4 (tools/exp_conv.py). */
 int srb_igemm_read_stamps(long long* out16);
 
-/* Bring-up microbenchmark: sustained tcgen05.mma issue rate (csrc/probe.cu); not on the product path. */
+/* 1 when the library was built with SRB_EXPERIMENTAL (opt-in filter-row / 2+1-tap convolution kernels and the probe
+ * below); the product build returns 0 and those kernels are absent. */
+int srb_has_experimental(void);
+
+/* Bring-up microbenchmark: sustained tcgen05.mma issue rate (csrc/probe.cu); SRB_EXPERIMENTAL builds only. */
 int srb_probe_mma_rate(int cta_group, int N, int iters, int a_row_shift, int mn_major, int b_lbo, int n_ctas,
                        long long* cycles_out, void* stream);
 

@@ -56,6 +56,10 @@ struct IgemmParams {
   uint32_t* sign_out; int sign_cstride, sign_coff;          // optional: (output > 0) bits, one word per 32 channels
   const uint32_t* mask_bits; int maskb_cstride, maskb_coff; // LRELU_MASK from sign words instead of `mask`
   float* colsum;    // optional [64]: per-channel sums of the stored outputs (bias gradient), n_ntiles == 1 only
+  int res_f32;      // bit 0 / 1: res1 / res2 are fp32 streams
+  float* y32; int y32_cstride, y32_coff;                    // optional fp32 copy of the output (plain store)
+  const __nv_bfloat16* res3; int res3_cstride, res3_coff; float res3_scale;
+  const float* chan_scale;                                  // optional [batch][cout] factor on (acc + bias)
   int base_offset_mode;
   int dbg;          // timing experiments only (flags >> 1): 1 no weight reloads, 2 no activation reloads, 4 no epilogue I/O
 };
@@ -125,6 +129,34 @@ __device__ __forceinline__ float warp_colsum32(const float (&v)[32], int lane) {
 
 template <bool COHERENT>
 __device__ __forceinline__ uint4 ld_row16(const uint4* p) { return COHERENT ? __ldcg(p) : __ldg(p); }
+template <bool COHERENT>
+__device__ __forceinline__ float4 ld_row16f(const float4* p) { return COHERENT ? __ldcg(p) : __ldg(p); }
+
+// v[32] += scale * (32 consecutive channels of a residual row): bf16 or fp32 source
+template <bool COHERENT>
+__device__ __forceinline__ void add_residual32(float (&v)[32], const void* base, size_t q, int cstride, int coff, int c0,
+                                               float scale, bool f32) {
+  if (f32) {
+    const float4* rp = reinterpret_cast<const float4*>(static_cast<const float*>(base) + q * cstride + coff + c0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 u = ld_row16f<COHERENT>(rp + i);
+      v[4 * i] += scale * u.x; v[4 * i + 1] += scale * u.y; v[4 * i + 2] += scale * u.z; v[4 * i + 3] += scale * u.w;
+    }
+  } else {
+    const uint4* rp = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(base) + q * cstride + coff + c0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint4 u = ld_row16<COHERENT>(rp + i);
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[8 * i + 2 * j] += scale * bf16lo(w[j]);
+        v[8 * i + 2 * j + 1] += scale * bf16hi(w[j]);
+      }
+    }
+  }
+}
 
 template <bool COHERENT = false>
 __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)[32], int q, int py, int px, int nt,
@@ -152,36 +184,22 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
       v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
     }
   }
+  if (p.chan_scale) {
+    const float4* cs4 = reinterpret_cast<const float4*>(p.chan_scale + static_cast<size_t>(q / p.P) * p.cout + c0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 c = __ldg(cs4 + i);
+      v[4 * i] *= c.x; v[4 * i + 1] *= c.y; v[4 * i + 2] *= c.z; v[4 * i + 3] *= c.w;
+    }
+  }
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] *= p.alpha;
-  if (p.res1) {
-    const uint4* rp = reinterpret_cast<const uint4*>(p.res1 + static_cast<size_t>(q) * p.res1_cstride +
-                                                     p.res1_coff + c0);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const uint4 u = ld_row16<COHERENT>(rp + i);
-      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        v[8 * i + 2 * j] += p.res1_scale * bf16lo(w[j]);
-        v[8 * i + 2 * j + 1] += p.res1_scale * bf16hi(w[j]);
-      }
-    }
-  }
-  if (p.res2) {
-    const uint4* rp = reinterpret_cast<const uint4*>(p.res2 + static_cast<size_t>(q) * p.res2_cstride +
-                                                     p.res2_coff + c0);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const uint4 u = ld_row16<COHERENT>(rp + i);
-      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        v[8 * i + 2 * j] += p.res2_scale * bf16lo(w[j]);
-        v[8 * i + 2 * j + 1] += p.res2_scale * bf16hi(w[j]);
-      }
-    }
-  }
+  if (p.res1) add_residual32<COHERENT>(v, p.res1, static_cast<size_t>(q), p.res1_cstride, p.res1_coff, c0, p.res1_scale,
+                                       p.res_f32 & 1);
+  if (p.res2) add_residual32<COHERENT>(v, p.res2, static_cast<size_t>(q), p.res2_cstride, p.res2_coff, c0, p.res2_scale,
+                                       p.res_f32 & 2);
+  if (p.res3) add_residual32<COHERENT>(v, p.res3, static_cast<size_t>(q), p.res3_cstride, p.res3_coff, c0, p.res3_scale,
+                                       false);
   if (p.act == SRB_ACT_LRELU) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.slope;
@@ -209,6 +227,11 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
 #pragma unroll
     for (int i = 0; i < 32; ++i) bits |= (v[i] > 0.f ? 1u : 0u) << i;
     p.sign_out[static_cast<size_t>(q) * p.sign_cstride + p.sign_coff + (c0 >> 5)] = bits;
+  }
+  if (p.y32) {
+    float4* y4 = reinterpret_cast<float4*>(p.y32 + static_cast<size_t>(q) * p.y32_cstride + p.y32_coff + c0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) y4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
   }
   uint4* yp = reinterpret_cast<uint4*>(p.y + yrow * p.y_cstride + ycoff + half * 32);
 #pragma unroll
@@ -523,6 +546,15 @@ int igemm_fill(const srb_conv3x3_args* a, const IgemmPlan& pl, IgemmParams* pp, 
   p.colsum = a->colsum;
   if (p.colsum && (a->cout != 64 || a->store_mode != SRB_STORE_PLAIN))
     return set_error("conv3x3: colsum needs cout == 64 and a plain store");
+  p.res_f32 = a->res_f32;
+  p.y32 = a->y32; p.y32_cstride = a->y32_cstride; p.y32_coff = a->y32_coff;
+  p.res3 = (const __nv_bfloat16*)a->res3; p.res3_cstride = a->res3_cstride; p.res3_coff = a->res3_coff; p.res3_scale = a->res3_scale;
+  p.chan_scale = a->chan_scale;
+  if ((p.y32 || p.chan_scale) && a->store_mode != SRB_STORE_PLAIN)
+    return set_error("conv3x3: y32 / chan_scale need a plain store");
+  if (p.y32 && ((a->y32_cstride | a->y32_coff) % 4)) return set_error("conv3x3: y32 stride / offset must keep 16-byte alignment");
+  if (((p.res_f32 & 1) && ((a->res1_cstride | a->res1_coff) % 4)) || ((p.res_f32 & 2) && ((a->res2_cstride | a->res2_coff) % 4)))
+    return set_error("conv3x3: fp32 residual stride / offset must keep 16-byte alignment");
   if (p.act == SRB_ACT_LRELU_MASK && !p.mask && !p.mask_bits)
     return set_error("conv3x3: mask activation without mask tensor");
   *pp = p;
@@ -541,7 +573,8 @@ int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
     if (conv_t21_plan(a, &pl21)) return conv3x3_chain_launch(a, 1, nullptr, 0, stream);    // else: image too wide for it
   }
   const bool want_row = (a->flags & 0x10000) || (conv_row_enabled() && !(a->flags & 0x20000));
-  if (want_row && ((a->flags >> 1) & 0x7fff) == 0 && !a->colsum && !a->sign_out && !a->mask_bits) {      // filter-row kernel (conv_row.cu); -1: geometry does not fit
+  if (want_row && ((a->flags >> 1) & 0x7fff) == 0 && !a->colsum && !a->sign_out && !a->mask_bits && !a->res_f32 &&
+      !a->y32 && !a->res3 && !a->chan_scale) {      // filter-row kernel (conv_row.cu); -1: geometry does not fit
     const int rc = conv3x3_row_launch(a, stream);
     if (rc >= 0) return rc;
   }

@@ -13,7 +13,14 @@ struct NaiveConvParams {
   const __nv_bfloat16* mask; int mask_cstride, mask_coff;
   const __nv_bfloat16* res1; int res1_cstride, res1_coff; float res1_scale;
   const __nv_bfloat16* res2; int res2_cstride, res2_coff; float res2_scale;
+  int res_f32; float* y32; int y32_cstride, y32_coff;
+  const __nv_bfloat16* res3; int res3_cstride, res3_coff; float res3_scale;
+  const float* chan_scale;
 };
+
+__device__ __forceinline__ float naive_res(const void* base, long long i, bool f32) {
+  return f32 ? static_cast<const float*>(base)[i] : __bfloat162float(static_cast<const __nv_bfloat16*>(base)[i]);
+}
 
 __global__ void conv3x3_naive_kernel(const NaiveConvParams p) {
   const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -35,9 +42,11 @@ __global__ void conv3x3_naive_kernel(const NaiveConvParams p) {
   }
   float v = acc;
   if (p.bias) v += p.bias[n];
+  if (p.chan_scale) v *= p.chan_scale[(q / p.P) * p.cout + n];
   v *= p.alpha;
-  if (p.res1) v += p.res1_scale * __bfloat162float(p.res1[q * p.res1_cstride + p.res1_coff + n]);
-  if (p.res2) v += p.res2_scale * __bfloat162float(p.res2[q * p.res2_cstride + p.res2_coff + n]);
+  if (p.res1) v += p.res1_scale * naive_res(p.res1, q * p.res1_cstride + p.res1_coff + n, p.res_f32 & 1);
+  if (p.res2) v += p.res2_scale * naive_res(p.res2, q * p.res2_cstride + p.res2_coff + n, p.res_f32 & 2);
+  if (p.res3) v += p.res3_scale * __bfloat162float(p.res3[q * p.res3_cstride + p.res3_coff + n]);
   if (p.act == SRB_ACT_LRELU) v = v > 0.f ? v : v * p.slope;
   else if (p.act == SRB_ACT_LRELU_MASK)
     v *= __bfloat162float(p.mask[q * p.mask_cstride + p.mask_coff + n]) > 0.f ? 1.f : p.slope;
@@ -49,6 +58,7 @@ __global__ void conv3x3_naive_kernel(const NaiveConvParams p) {
     p.y[yrow * p.y_cstride + p.y_coff + c] = __float2bfloat16(v);
   } else {
     p.y[q * p.y_cstride + p.y_coff + n] = __float2bfloat16(v);
+    if (p.y32) p.y32[q * p.y32_cstride + p.y32_coff + n] = v;
   }
 }
 
@@ -67,6 +77,11 @@ int conv3x3_naive_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   p.mask = (const __nv_bfloat16*)a->mask; p.mask_cstride = a->mask_cstride; p.mask_coff = a->mask_coff;
   p.res1 = (const __nv_bfloat16*)a->res1; p.res1_cstride = a->res1_cstride; p.res1_coff = a->res1_coff; p.res1_scale = a->res1_scale;
   p.res2 = (const __nv_bfloat16*)a->res2; p.res2_cstride = a->res2_cstride; p.res2_coff = a->res2_coff; p.res2_scale = a->res2_scale;
+  p.res_f32 = a->res_f32; p.y32 = a->y32; p.y32_cstride = a->y32_cstride; p.y32_coff = a->y32_coff;
+  p.res3 = (const __nv_bfloat16*)a->res3; p.res3_cstride = a->res3_cstride; p.res3_coff = a->res3_coff; p.res3_scale = a->res3_scale;
+  p.chan_scale = a->chan_scale;
+  if ((p.y32 || p.chan_scale) && a->store_mode != SRB_STORE_PLAIN)
+    return set_error("conv3x3(naive): y32 / chan_scale need a plain store");
   const long long total = 1LL * p.R * p.cout;
   conv3x3_naive_kernel<<<ceil_div(total, 256), 256, 0, stream>>>(p);
   cudaError_t e = cudaGetLastError();

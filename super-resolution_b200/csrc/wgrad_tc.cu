@@ -10,9 +10,18 @@
 //   B = GZ window [K = 64 pixels][N = 192 = 3 x 64]        the three 64-wide N blocks are the SAME smem
 //       window advanced by one pixel row each (LBO = 128 B): N block j is tap dx = 1 - j.  One MMA therefore
 //       produces three taps of one filter row; dy selects the window's row offset.
-// Work item = (pair of input-channel blocks, dy, 64-wide output-channel block, K split).  Each CTA accumulates
-// its whole K range in 192 TMEM columns, then writes a partial [3 taps][128 ci][64 co] fp32 tile to the
-// workspace; a second kernel reduces the K splits, scales, and scatters to OIHW (state_dict layout).
+// The M = 128 rows of an MMA are two independent 64-row halves that only have to share the B window.  A unit fills them
+// in one of two ways (round 2; before, a unit was a pair of ADJACENT input-channel blocks for one dy, which left half
+// of the M tile empty on every odd 64-channel block: 17 % of the MMAs of a dense block):
+//   row-pair unit (one per 64-channel input block c):  half 0 = X[q][c], half 1 = X[q + pitch][c] against the dy = -1
+//       window - half 1 then IS the dy = 0 tap row (sum_q X[q+pitch] GZ[q+pitch-1+j] = sum_q' X[q'] GZ[q'-1+j]);
+//   block-pair unit (one per two input blocks c, c'):  half 0 = X[q][c], half 1 = X[q][c'] against the dy = +1 window.
+// A dense block (cin = 64..320) takes 24 units instead of 27, with three idle halves instead of nine; 148 / 24 gives
+// 6 K splits = 144 CTAs (was 5 x 27 = 135).  The K range starts ceil(pitch / 64) chunks before row 0 so that the
+// shifted half sees the first image row (rows < 0 are TMA out-of-bounds zeros).
+// Work item = (unit, 64-wide output-channel block, K split).  Each CTA accumulates its whole K range in 192 TMEM
+// columns per issuer, then writes partial [3 taps][64 ci][64 co] fp32 tiles (one per half) to the workspace; a second
+// kernel reduces the K splits, scales, and scatters to OIHW (state_dict layout).
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -32,12 +41,13 @@ constexpr int kWgStageBytes = kWgXBytes + kWgGBytes;
 struct WgradParams {
   int R, pitch;
   int cin, cout;
-  int n_cp;          // ceil(cin / 128)
+  int nk;            // cin / 64
   int n_cb;          // cout / 64
+  int lead;          // chunks in front of row 0 (ceil(pitch / 64))
   int splits;        // K splits
   int chunks_per_split;
   int x_coff, gy_coff;
-  float* ws;         // [splits][9][n_cp*128][cout]
+  float* ws;         // [splits][9][cin][cout]
   int base_offset_mode;
   float alpha;
   int unshuffle;
@@ -51,7 +61,7 @@ constexpr int kWgColsumFloats = 2048;           // widest gradient buffer the bi
 struct WgradGroup {
   int n, splits;
   int dbg;                           // timing experiments (SRB_WGRAD_DBG): 1 = operands loaded for the first ring pass only
-  int unit_start[kWgMaxGroup + 1];   // first (cp, cb, dy) unit of every problem
+  int unit_start[kWgMaxGroup + 1];   // first (unit, cb) work item of every problem
   WgradParams prob[kWgMaxGroup];
 };
 
@@ -74,11 +84,13 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
   while (pi + 1 < g.n && unit >= g.unit_start[pi + 1]) ++pi;
   const WgradParams& p = g.prob[pi];
   int w = unit - g.unit_start[pi];
-  const int dyi = w % 3; w /= 3;                 // dy = dyi - 1
   const int cb = w % p.n_cb; w /= p.n_cb;
-  const int cp = w;
-  const int dy = dyi - 1;
-  const int n_chunks_total = (p.R + kWgKc - 1) / kWgKc;
+  // halves of the M tile: input block, row shift of its X rows, tap row (dy + 1) it produces; dyB = dy of the B window
+  int c0, c1, shift1, dyi0, dyi1, dyB;
+  if (w < p.nk) { c0 = w; c1 = w; shift1 = p.pitch; dyi0 = 0; dyi1 = 1; dyB = -1; }
+  else { const int v = w - p.nk; c0 = 2 * v; c1 = 2 * v + 1; shift1 = 0; dyi0 = 2; dyi1 = 2; dyB = 1; }
+  const bool has1 = c1 < p.nk;
+  const int n_chunks_total = p.lead + (p.R + kWgKc - 1) / kWgKc;
   const int c_begin = split * p.chunks_per_split;
   int c_end = c_begin + p.chunks_per_split;
   if (c_end > n_chunks_total) c_end = n_chunks_total;
@@ -103,14 +115,14 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
     if (elect_one()) {   // elect.sync: ptxas then keeps descriptors and barrier addresses in uniform registers
       uint32_t s = 0, ph = 0;
       for (int c = 0; c < n_chunks; ++c) {
-        const int k0 = (c_begin + c) * kWgKc;
+        const int k0 = (c_begin + c - p.lead) * kWgKc;
         mbar_wait(&empty[s], ph ^ 1, 11);
         if ((g.dbg & 1) && c >= kWgStages) { mbar_arrive(&full[s]); if (++s == kWgStages) { s = 0; ph ^= 1; } continue; }
-        mbar_expect_tx(&full[s], kWgStageBytes);
+        mbar_expect_tx(&full[s], has1 ? kWgStageBytes : kWgStageBytes - kWgKc * 128);
         uint8_t* st = smem + s * kWgStageBytes;
-        tma_load_2d(st, &tmap_x, p.x_coff + cp * 128, k0, &full[s]);
-        tma_load_2d(st + kWgKc * 128, &tmap_x, p.x_coff + cp * 128 + 64, k0, &full[s]);
-        tma_load_2d(st + kWgXBytes, &tmap_g, p.gy_coff + cb * 64, k0 - dy * p.pitch - 1, &full[s]);
+        tma_load_2d(st, &tmap_x, p.x_coff + c0 * 64, k0, &full[s]);
+        if (has1) tma_load_2d(st + kWgKc * 128, &tmap_x, p.x_coff + c1 * 64, k0 + shift1, &full[s]);
+        tma_load_2d(st + kWgXBytes, &tmap_g, p.gy_coff + cb * 64, k0 - dyB * p.pitch - 1, &full[s]);
         if (++s == kWgStages) { s = 0; ph ^= 1; }
       }
     }
@@ -143,17 +155,20 @@ wgrad3x3_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_cons
     }
   } else {
     const int lg = warp & 3;
-    const int row = lg * 32 + lane;               // M index = input channel within the pair
-    const int ci = cp * 128 + row;
-    const int cin_pad = p.n_cp * 128;
+    const int row = lg * 32 + lane;               // M index: half = row / 64, input channel within the block = row % 64
+    const int hf = row >> 6;
+    const int ci = (hf ? c1 : c0) * 64 + (row & 63);
+    const int dyi = hf ? dyi1 : dyi0;
     if (n_chunks > 0) {
       mbar_wait(done, 0, 13);
       tc_fence_after();
     }
+    const bool live = !hf || has1;                // warp-uniform (a warp lies inside one half)
 #pragma unroll 1
     for (int j = 0; j < 3; ++j) {
+      if (!live) break;
       const int t = dyi * 3 + (2 - j);            // dx = 1 - j  ->  kx = dx + 1 = 2 - j
-      float* dst = p.ws + ((static_cast<size_t>(split) * 9 + t) * cin_pad + ci) * p.cout + cb * 64;
+      float* dst = p.ws + ((static_cast<size_t>(split) * 9 + t) * p.cin + ci) * p.cout + cb * 64;
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         uint32_t acc[32], acc2[32];
@@ -253,15 +268,16 @@ __global__ void wgrad_reduce_kernel(const __grid_constant__ ReduceGroup rg) {
   }
 }
 
-static void wgrad_group_plan(long long R, int n, const int* cin, const int* cout, int* splits, int* chunks_per_split,
-                             int* unit_start) {
+static void wgrad_group_plan(long long R, int pitch, int n, const int* cin, const int* cout, int* splits,
+                             int* chunks_per_split, int* unit_start) {
   int units = 0;
   for (int i = 0; i < n; ++i) {
     unit_start[i] = units;
-    units += ((cin[i] + 127) / 128) * (cout[i] / 64) * 3;
+    const int nk = cin[i] / 64;
+    units += (nk + (nk + 1) / 2) * (cout[i] / 64);     // row-pair units + block-pair units, per 64-wide output block
   }
   unit_start[n] = units;
-  const int chunks = int((R + kWgKc - 1) / kWgKc);
+  const int chunks = (pitch + kWgKc - 1) / kWgKc + int((R + kWgKc - 1) / kWgKc);
   int s = sm_count() / units;                         // one CTA per SM (150 KB of smem each), one wave, no tail wave
   if (s < 1) s = 1;
   const int max_s = (chunks + 7) / 8;                 // at least 8 chunks per split
@@ -276,7 +292,7 @@ static size_t wgrad_group_ws(int n, const int* cin, const int* cout, int splits,
   size_t total = 0;
   for (int i = 0; i < n; ++i) {
     if (offs) offs[i] = total;
-    total += static_cast<size_t>(splits) * 9 * ((cin[i] + 127) / 128) * 128 * cout[i];
+    total += static_cast<size_t>(splits) * 9 * cin[i] * cout[i];
   }
   return (total + kWgColsumFloats) * sizeof(float);   // + column sums of the gradient buffer (bias gradients)
 }
@@ -301,7 +317,7 @@ int wgrad3x3_tc_launch_group(const srb_wgrad3x3_args* a, int n, cudaStream_t str
   }
   WgradGroup g{};
   int splits, cps;
-  wgrad_group_plan(R, n, cin, cout, &splits, &cps, g.unit_start);
+  wgrad_group_plan(R, pitch, n, cin, cout, &splits, &cps, g.unit_start);
   size_t offs[kWgMaxGroup];
   const size_t need = wgrad_group_ws(n, cin, cout, splits, offs);
   if (!a0.workspace || a0.workspace_bytes < need) return set_error("wgrad3x3: workspace too small");
@@ -325,11 +341,11 @@ int wgrad3x3_tc_launch_group(const srb_wgrad3x3_args* a, int n, cudaStream_t str
     const srb_wgrad3x3_args& ai = a[i];
     WgradParams& p = g.prob[i];
     p.R = (int)R; p.pitch = pitch; p.cin = ai.cin; p.cout = ai.cout;
-    p.n_cp = (ai.cin + 127) / 128; p.n_cb = ai.cout / 64;
+    p.nk = ai.cin / 64; p.n_cb = ai.cout / 64; p.lead = (pitch + kWgKc - 1) / kWgKc;
     p.splits = splits; p.chunks_per_split = cps; p.x_coff = ai.x_coff; p.gy_coff = ai.gy_coff;
     p.ws = (float*)a0.workspace + offs[i]; p.base_offset_mode = 0;
     p.alpha = ai.alpha; p.unshuffle = ai.unshuffle;
-    rg.it[i] = ReduceItem{p.ws, ai.dw, ai.cin, p.n_cp * 128, ai.cout, ai.alpha,
+    rg.it[i] = ReduceItem{p.ws, ai.dw, ai.cin, ai.cin, ai.cout, ai.alpha,
                           ai.dbias ? colsum + ai.gy_coff : nullptr, ai.dbias};
     any_bias = any_bias || ai.dbias != nullptr;
     const long long tot = 9LL * ai.cin * ai.cout;
@@ -366,14 +382,14 @@ int wgrad3x3_tc_launch(const srb_wgrad3x3_args* a, cudaStream_t stream) { return
 
 extern "C" size_t srb_wgrad3x3_workspace_bytes(int batch, int H, int W, int cin, int cout) {
   int splits, cps, us[srb::kWgMaxGroup + 1];
-  srb::wgrad_group_plan(1LL * batch * (H + 1) * (W + 1), 1, &cin, &cout, &splits, &cps, us);
+  srb::wgrad_group_plan(1LL * batch * (H + 1) * (W + 1), W + 1, 1, &cin, &cout, &splits, &cps, us);
   return srb::wgrad_group_ws(1, &cin, &cout, splits, nullptr);
 }
 
 extern "C" size_t srb_wgrad3x3_group_workspace_bytes(int batch, int H, int W, int n, const int* cin, const int* cout) {
   if (n < 1 || n > srb::kWgMaxGroup) return 0;
   int splits, cps, us[srb::kWgMaxGroup + 1];
-  srb::wgrad_group_plan(1LL * batch * (H + 1) * (W + 1), n, cin, cout, &splits, &cps, us);
+  srb::wgrad_group_plan(1LL * batch * (H + 1) * (W + 1), W + 1, n, cin, cout, &splits, &cps, us);
   return srb::wgrad_group_ws(n, cin, cout, splits, nullptr);
 }
 

@@ -38,6 +38,9 @@ class Conv3x3Args(C.Structure):
         ("sign_out", C.c_void_p), ("sign_cstride", C.c_int), ("sign_coff", C.c_int),
         ("mask_bits", C.c_void_p), ("maskb_cstride", C.c_int), ("maskb_coff", C.c_int),
         ("colsum", C.c_void_p),
+        ("res_f32", C.c_int), ("y32", C.c_void_p), ("y32_cstride", C.c_int), ("y32_coff", C.c_int),
+        ("res3", C.c_void_p), ("res3_cstride", C.c_int), ("res3_coff", C.c_int), ("res3_scale", C.c_float),
+        ("chan_scale", C.c_void_p),
     ]
 
 
@@ -76,11 +79,16 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB_PATH
     nvcc = os.environ.get("NVCC", "nvcc")
+    tmp = LIB_PATH + ".tmp%d" % os.getpid()          # never leave a half-written library where lib() would load it
     cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-          ["-o", LIB_PATH, os.path.join(CSRC, "srb200_all.cu")]
+          (["-DSRB_EXPERIMENTAL"] if os.environ.get("SRB_EXPERIMENTAL") == "1" else []) + \
+          ["-o", tmp, os.path.join(CSRC, "srb200_all.cu")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
+        if os.path.exists(tmp):
+            os.remove(tmp)
         raise RuntimeError("CUDA extension build failed:\n" + r.stdout + r.stderr)
+    os.replace(tmp, LIB_PATH)
     if verbose:
         print(r.stderr)
     return LIB_PATH
@@ -92,6 +100,7 @@ _lock = threading.Lock()
 _SIGS = {
     "srb_last_error": (C.c_char_p, []),
     "srb_abi_version": (C.c_int, []),
+    "srb_has_experimental": (C.c_int, []),
     "srb_read_fault": (C.c_int, [C.POINTER(C.c_uint)]),
     "srb_conv3x3": (C.c_int, [C.POINTER(Conv3x3Args), C.c_void_p]),
     "srb_conv3x3_chain": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
@@ -179,8 +188,8 @@ def lib():
                     fn = getattr(l, name)
                     fn.restype = res
                     fn.argtypes = args
-                if l.srb_abi_version() != 2:
-                    raise RuntimeError("CUDA extension libsrb200.so is stale (ABI %d, bindings expect 2): rebuild it"
+                if l.srb_abi_version() != 3:
+                    raise RuntimeError("CUDA extension libsrb200.so is stale (ABI %d, bindings expect 3): rebuild it"
                                        % l.srb_abi_version())
                 _lib = l
     return _lib

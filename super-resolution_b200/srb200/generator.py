@@ -85,6 +85,11 @@ class GeneratorEngine:
         self._saved = None
         self._fwd_gen = 0            # forward(save_for_backward=True) counter: backward must match the LAST such forward
         self._bias_perm = {}
+        # The residual stream of the RRDB trunk (x_{d+1} = x_d + 0.2 conv5(...), models.py:41,53) is carried in fp32 next
+        # to the bf16 copy the next convolution reads.  With a bf16-only stream its 3 nb roundings accumulate: rel-L2
+        # 2.25e-2 / energy 5.3e-3 at nb = 23 against SURVEY 8c's 2e-2 / 5e-3; with the fp32 stream 1.3e-2 / 2.6e-3
+        # (DESIGN.md section 2).
+        self.fp32_stream = True
         self.grad_views = None       # optional name -> fp32 view: where backward writes parameter gradients
         self.ready_hook = None       # optional callable(param_name): gradients of this and all later parameters are final
         self.names3x3 = self._conv_names()
@@ -234,6 +239,7 @@ class GeneratorEngine:
         n_growth = 3 * self.nb if training else 4
         bf.growth = [ops.pnhwc_zeros(B, h, w, 5 * F_, dev) for _ in range(max(n_growth, 1))]
         bf.out1 = None if training else ops.pnhwc_zeros(B, h, w, F_, dev)
+        bf.xs = [torch.zeros(B, h + 1, w + 1, F_, dtype=torch.float32, device=dev) for _ in range(4)]
         bf.trunk = ops.pnhwc_zeros(B, h, w, F_, dev)
         bf.feat = ops.pnhwc_zeros(B, h, w, F_, dev)
         bf.up = [ops.pnhwc_zeros(B, h << (u + 1), w << (u + 1), F_, dev) for u in range(self.nup)]
@@ -340,11 +346,17 @@ class GeneratorEngine:
                          sign_out=(sign, 2 * (k - 1)) if sign is not None else None)
                 last = (i == self.nb - 1 and j == 2)
                 dst, dst_off = (bf.trunk, 0) if last else (g[(d + 1) % ng], 0)
+                # fp32 residual stream: block d reads it from xs[d % 4] (block 0: conv1's bf16 output) and leaves the
+                # next one in xs[(d + 1) % 4]; the RRDB's own input stays in xs[first % 4] for the outer skip
+                fs = self.fp32_stream
+                s_in = bf.xs[d % 4] if (fs and d > 0) else cur
+                s_first = bf.xs[first % 4] if (fs and first > 0) else g[first % ng]
+                y32 = (bf.xs[(d + 1) % 4], 0) if (fs and not last) else None
                 if j < 2:
-                    conv(cur, 0, 5 * F_, base + "b5.0", dst, dst_off, F_, alpha=DRB_SCALE, res1=(cur, 0, 1.0))
+                    conv(cur, 0, 5 * F_, base + "b5.0", dst, dst_off, F_, alpha=DRB_SCALE, res1=(s_in, 0, 1.0), y32=y32)
                 else:
                     conv(cur, 0, 5 * F_, base + "b5.0", dst, dst_off, F_, alpha=DRB_SCALE * self.rs,
-                         res1=(cur, 0, self.rs), res2=(g[first % ng], 0, 1.0))
+                         res1=(s_in, 0, self.rs), res2=(s_first, 0, 1.0), y32=y32)
                 d += 1
                 if chain and len(pend) + 5 > chain:
                     self._flush(pend, bf.flags_f, B, h, w)

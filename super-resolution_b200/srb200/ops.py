@@ -97,7 +97,8 @@ def conv3x3_args(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Te
                  mask: Optional[Tuple[Tensor, int]] = None, res1: Optional[Tuple[Tensor, int, float]] = None,
                  res2: Optional[Tuple[Tensor, int, float]] = None, shuffle: bool = False, impl: int = L.IMPL_TCGEN05,
                  flags: int = 0, colsum: Optional[Tensor] = None, sign_out: Optional[Tuple[Tensor, int]] = None,
-                 mask_bits: Optional[Tuple[Tensor, int]] = None):
+                 mask_bits: Optional[Tuple[Tensor, int]] = None, y32: Optional[Tuple[Tensor, int]] = None,
+                 res3: Optional[Tuple[Tensor, int, float]] = None, chan_scale: Optional[Tensor] = None):
     """srb_conv3x3_args for y[..., y_coff:y_coff+cout] = epilogue(conv3x3(x[..., x_coff:x_coff+cin])) and its
     algorithmic FLOPs; x, y PNHWC bf16 buffers."""
     _require_cuda(x, "conv3x3")
@@ -115,10 +116,25 @@ def conv3x3_args(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Te
     a.alpha, a.act, a.slope = alpha, act, slope
     if mask is not None:
         a.mask, a.mask_cstride, a.mask_coff = mask[0].data_ptr(), mask[0].shape[-1], mask[1]
-    if res1 is not None:
+    f32 = 0
+    if res1 is not None:     # (tensor, channel offset, scale): bf16 PNHWC, or an fp32 buffer of the same geometry
         a.res1, a.res1_cstride, a.res1_coff, a.res1_scale = res1[0].data_ptr(), res1[0].shape[-1], res1[1], res1[2]
+        assert res1[0].dtype in (torch.bfloat16, torch.float32) and res1[0].shape[:3] == x.shape[:3]
+        f32 |= 1 if res1[0].dtype == torch.float32 else 0
     if res2 is not None:
         a.res2, a.res2_cstride, a.res2_coff, a.res2_scale = res2[0].data_ptr(), res2[0].shape[-1], res2[1], res2[2]
+        assert res2[0].dtype in (torch.bfloat16, torch.float32) and res2[0].shape[:3] == x.shape[:3]
+        f32 |= 2 if res2[0].dtype == torch.float32 else 0
+    a.res_f32 = f32
+    if res3 is not None:
+        assert res3[0].dtype == torch.bfloat16 and res3[0].shape[:3] == x.shape[:3]
+        a.res3, a.res3_cstride, a.res3_coff, a.res3_scale = res3[0].data_ptr(), res3[0].shape[-1], res3[1], res3[2]
+    if y32 is not None:      # (fp32 tensor of y's pixel geometry, channel offset): unrounded copy of the output
+        assert y32[0].dtype == torch.float32 and y32[0].shape[:3] == y.shape[:3] and not shuffle
+        a.y32, a.y32_cstride, a.y32_coff = y32[0].data_ptr(), y32[0].shape[-1], y32[1]
+    if chan_scale is not None:   # fp32 [batch, cout]
+        assert chan_scale.dtype == torch.float32 and tuple(chan_scale.shape) == (B, cout) and chan_scale.is_contiguous()
+        a.chan_scale = chan_scale.data_ptr()
     a.impl, a.flags = impl, flags
     if sign_out is not None:    # (int32 [B, H+1, W+1, words], first word): (output > 0) bits, 32 channels per word
         assert sign_out[0].dtype == torch.int32 and sign_out[0].shape[:3] == y.shape[:3]

@@ -68,7 +68,10 @@ def write_txt_dataset(path, hits):
 
 
 def run(ref_root, models_dir=None, *, n_batches=20, batch_size=16, seed=4321, factor=4, residual_blocks=10,
-        overrides=None, quiet=True):
+        overrides=None, quiet=True, preload=False):
+    """``preload``: build every dataset item once before train() starts and serve it from memory afterwards, so the
+    per-step times in the result (``step_t``: perf_counter at the first gradient-penalty draw of each step) measure
+    the training iteration, not np.loadtxt (bench.py's reference arm uses this)."""
     import torch
     ref_root = os.path.abspath(ref_root)
     if not os.path.isdir(ref_root):
@@ -90,13 +93,15 @@ def run(ref_root, models_dir=None, *, n_batches=20, batch_size=16, seed=4321, fa
         def __init__(self, optimizer, *a, verbose=None, **kw):
             super().__init__(optimizer, *a, **kw)
 
-    rec = {"epsilons": [], "order": []}
+    import time as _time
+    rec = {"epsilons": [], "order": [], "t": []}
     real_rand = torch.rand
 
     def rec_rand(*a, **kw):
         t = real_rand(*a, **kw)
         if t.dim() == 4 and t.shape[1:] == (1, 1, 1):       # esrgan.py:598
             rec["epsilons"].append(t.reshape(-1).tolist())
+            rec["t"].append(_time.perf_counter())
         return t
 
     try:
@@ -117,10 +122,17 @@ def run(ref_root, models_dir=None, *, n_batches=20, batch_size=16, seed=4321, fa
                 cls = type(ds)
                 real_item = cls.__getitem__
 
+                cache = {}
+
                 class Recording(cls):
                     def __getitem__(self, i):
                         rec["order"].append(int(i))
+                        if i in cache:
+                            return {k: v.clone() for k, v in cache[i].items()}
                         return real_item(self, i)
+                if preload:
+                    for i in range(len(ds)):
+                        cache[i] = real_item(ds, i)
                 ds.__class__ = Recording
                 return ds
 
@@ -156,6 +168,7 @@ def run(ref_root, models_dir=None, *, n_batches=20, batch_size=16, seed=4321, fa
         if not loss:
             raise RuntimeError("reference train() returned no loss trace")
         return {"loss": loss, "order": rec["order"], "epsilons": rec["epsilons"], "init_checksums": sums,
+                "step_t": rec["t"][0::2],
                 "cfg": dict(n_batches=n_batches, batch_size=batch_size, seed=seed, factor=factor,
                             residual_blocks=residual_blocks, overrides=overrides or {}),
                 "models_file": models_file, "device": "cuda" if torch.cuda.is_available() else "cpu",

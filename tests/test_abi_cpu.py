@@ -16,7 +16,7 @@ def test_library_exports_declared_symbols():
     from srb200 import _lib as L
     L.build()
     lib = L.lib()
-    assert lib.srb_abi_version() == 2
+    assert lib.srb_abi_version() == 3
     hdr = open(os.path.join(ROOT, "include", "srb200.h")).read()
     declared = set(re.findall(r"\b(srb_[a-z0-9_]+)\s*\(", hdr))
     assert declared, "header declares no entry points?"

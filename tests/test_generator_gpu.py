@@ -173,6 +173,9 @@ def test_taps_2_1_kernel_forward_backward_vs_oracle(batch, lr_size, nup, nb):
     """the 2+1-tap convolution kernel (csrc/conv_chain21.cu, opt-in) through the whole generator: same tolerances as
     the default kernels against the fp32 oracle."""
     dev = _dev()
+    from srb200 import _lib as L
+    if not L.lib().srb_has_experimental():
+        pytest.skip("the 2+1-tap kernel is compiled in SRB_EXPERIMENTAL builds only")
     cfg = dict(nb=nb, nup=nup, power=1.0, multiplier=1.0, res_scale=0.1, seed=31, gain=1.2, thres=0.0, training=True)
     g, sd = _build(cfg, dev)
     g._engine().conv_flags = 0x100000

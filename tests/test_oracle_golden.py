@@ -92,3 +92,21 @@ def test_adam_matches_torch():
         opt.step()
         O.adam_step(q, grad, m, v, step, weight_decay=0.01)
         torch.testing.assert_close(q, p.detach(), rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("name", ["nb10_x4", "nb23_x8"])
+def test_oracle_matches_reference_at_benchmarked_depth(name):
+    """golden_v2.pt (tests/golden/make_golden_v2.py): the reference modules at nb = 10 / x4 and nb = 23 / x8.  Inference
+    is per-image, so the oracle is checked on the stored images only (seconds on the CPU)."""
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    case = torch.load(os.path.join(root, "tests", "golden", "golden_v2.pt"), weights_only=False)[name]
+    cfg = case["cfg"]
+    sd = O.make_generator_sd(cfg["seed"], num_res_blocks=cfg["nb"], num_upsample=cfg["nup"], gain=cfg["gain"])
+    batch = cfg.get("batch", cfg.get("batch_eval"))
+    _, lr = O.synthetic_jets(batch, 80, 2 ** cfg["nup"], cfg["data_seed"])
+    with torch.no_grad():
+        out, srs = O.generator_forward(sd, lr[case["sel"]], res_scale=cfg["res_scale"], thres=0.0, training=False)
+    torch.testing.assert_close(out, case["eval_out"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(srs, case["eval_srs"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(out.sum((1, 2, 3)), case["eval_energy"][case["sel"]], rtol=1e-4, atol=1e-4)

@@ -47,37 +47,43 @@ def _ref_models():
 
 
 class _FunctionalG(torch.nn.Module):
-    """oracle.generator_forward as a module (used only when baseline/_ref is absent)."""
+    """oracle.generator_forward as a module: the same ATen calls as the reference's GeneratorRRDB.forward, but `power` /
+    `multiplier` stay host scalars, so the forward has none of the reference's .item() synchronisations
+    (models.py:116,118,133) and CAN be captured in a CUDA graph.  Used for the cuda_graph rows (the reference modules
+    themselves cannot be captured) and when baseline/_ref is absent."""
 
     def __init__(self, sd, nb, nup):
         super().__init__()
-        self.names = list(sd)
-        self.ps = torch.nn.ParameterList([torch.nn.Parameter(v.clone(), requires_grad=k not in ("power", "multiplier"))
-                                          for k, v in sd.items()])
+        self.names = [k for k in sd if k not in ("power", "multiplier")]
+        self.ps = torch.nn.ParameterList([torch.nn.Parameter(sd[k].clone()) for k in self.names])
+        self.host = {k: sd[k].clone() for k in ("power", "multiplier")}      # CPU tensors: .item() costs no device sync
         self.thres = 0.0
 
     def forward(self, x):
         sd = dict(zip(self.names, self.ps))
+        sd.update(self.host)
         out, self.srs = O.generator_forward(sd, x, res_scale=RES_SCALE, thres=0.0, training=self.training)
         return out
 
 
-def build(dev, nb=NB, nup=NUP, channels_last=False):
+def build(dev, nb=NB, nup=NUP, channels_last=False, sync_free=False):
     R = _ref_models()
     sd = O.make_generator_sd(1234, num_res_blocks=nb, num_upsample=nup)
+    Ds = None
     if R is not None:
-        G = R.GeneratorRRDB(1, filters=64, num_res_blocks=nb, num_upsample=nup, res_scale=RES_SCALE)
-        G.load_state_dict(sd)
         Ds = []
         for k in range(2):
             d = R.Markovian_Discriminator((1, HR, HR), [16, 32, 32, 64])
             d.load_state_dict(O.make_discriminator_sd(1235 + k, gain=2.0))
             Ds.append(d)
+    if R is not None and not sync_free:
+        G = R.GeneratorRRDB(1, filters=64, num_res_blocks=nb, num_upsample=nup, res_scale=RES_SCALE)
+        G.load_state_dict(sd)
         kind = "reference modules (baseline/_ref/models.py)"
     else:
         G = _FunctionalG(sd, nb, nup)
-        Ds = None
-        kind = "functional port (oracle/oracle.py)"
+        kind = "functional port of the generator without the reference's .item() syncs (oracle/oracle.py)" + \
+               ("" if R is None else " + reference discriminator modules")
     G = G.to(dev)
     if Ds is not None:
         Ds = [d.to(dev) for d in Ds]
@@ -181,7 +187,7 @@ def graphed(fn, warmup=3):
 def measure(dev, batch, precision, workload, use_graph, steps=5, warmup=3, nb=NB, nup=NUP, factor=FACTOR):
     """images/s of one (batch, precision, workload, launch) point; None + reason when it cannot run."""
     cl = precision == "bf16_channels_last"
-    G, Ds, kind = build(dev, nb, nup, channels_last=cl)
+    G, Ds, kind = build(dev, nb, nup, channels_last=cl, sync_free=use_graph)
     hr, lr = O.synthetic_jets(batch, HR, factor, 1234)
     hr, lr = hr.to(dev), lr.to(dev)
     if cl:
@@ -203,7 +209,7 @@ def measure(dev, batch, precision, workload, use_graph, steps=5, warmup=3, nb=NB
             G.train()
             fn = gan_step_factory(G, Ds, hr, lr, ctx, capturable=use_graph, gate=not use_graph)
         if use_graph:
-            fn = graphed(fn)
+            fn = graphed(fn, warmup=2)
         ms = timed(fn, steps, 0 if use_graph else warmup)
         return {"images_per_s": batch / (ms * 1e-3), "ms_per_step": ms, "impl": kind}, None
     except Exception as e:  # noqa: BLE001   (OOM / capture failure: reported, not fatal)
@@ -213,17 +219,33 @@ def measure(dev, batch, precision, workload, use_graph, steps=5, warmup=3, nb=NB
         torch.cuda.empty_cache()
 
 
+def run_point(dev, wl, prec, use_graph, b, steps):
+    t0 = time.time()
+    res, err = measure(dev, b, prec, wl, use_graph, steps=steps)
+    row = {"workload": wl, "precision": prec, "launch": "cuda_graph" if use_graph else "eager", "batch": b,
+           "wall_s": round(time.time() - t0, 1)}
+    row.update(res if res is not None else {"unavailable": err})
+    return row
+
+
 def run_matrix(dev, batches, precisions, workloads, launches, steps=5):
+    """Eager points run in this process.  Every cuda_graph point runs in its OWN subprocess: a capture that fails (or
+    runs out of memory) leaves the RNG / allocator of its process unusable for the points after it."""
+    import subprocess
     rows = []
     for wl in workloads:
         for prec in precisions:
             for use_graph in launches:
                 for b in batches:
-                    t0 = time.time()
-                    res, err = measure(dev, b, prec, wl, use_graph, steps=steps)
-                    row = {"workload": wl, "precision": prec, "launch": "cuda_graph" if use_graph else "eager",
-                           "batch": b, "wall_s": round(time.time() - t0, 1)}
-                    row.update(res if res is not None else {"unavailable": err})
+                    if not use_graph:
+                        row = run_point(dev, wl, prec, False, b, steps)
+                    else:
+                        r = subprocess.run([sys.executable, os.path.abspath(__file__), "--point",
+                                            f"{wl},{prec},{b},{steps}"], capture_output=True, text=True, timeout=600)
+                        lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+                        row = json.loads(lines[-1]) if lines else {
+                            "workload": wl, "precision": prec, "launch": "cuda_graph", "batch": b,
+                            "unavailable": "subprocess failed: " + (r.stderr.strip().splitlines() or ["?"])[-1][:200]}
                     rows.append(row)
                     print(json.dumps(row), flush=True)
     return rows
@@ -233,9 +255,14 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=None)
     ap.add_argument("--quick", action="store_true", help="batch 512 only, eager + graph, 3 steps")
+    ap.add_argument("--point", default=None, help="internal: workload,precision,batch,steps of one cuda_graph point")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
+    if a.point:
+        wl, prec, b, steps = a.point.split(",")
+        print(json.dumps(run_point(dev, wl, prec, True, int(b), int(steps))), flush=True)
+        return
     batches = [512] if a.quick else [16, 64, 512]
     rows = run_matrix(dev, batches, ["fp32", "bf16_channels_last"], ["inference", "generator_train", "gan_step"],
                       [False, True], steps=3 if a.quick else 5)
