@@ -10,7 +10,7 @@ from torch.profiler import profile, ProfilerActivity
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 dev = torch.device("cuda:0")
-G, Ds = bench.build_models(dev)
+G, Ds = bench.build_models(dev, bench.CONFIGS['gan'])
 tr = GANTrainStep(G, Ds, factor=4)
 hr, lr = O.synthetic_jets(B, 80, 4, 1)
 hr, lr = hr.to(dev), lr.to(dev)
@@ -24,5 +24,5 @@ rows = [(e.key, e.device_time_total / 1e3, e.count) for e in prof.key_averages()
 rows.sort(key=lambda r: -r[1])
 tot = sum(r[1] for r in rows if "srb" in r[0] or "kernel" in r[0].lower())
 print(f"batch {B}")
-for k, ms, n in rows[:40]:
+for k, ms, n in rows[:60]:
     print(f"{ms:9.3f} ms  {n:5d}x  {k[:110]}")
