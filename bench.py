@@ -220,11 +220,19 @@ def time_reference_train(batch, steps, warmup, cfg):
     its own esrgan.train() on the host cores: tests/ref_harness.py supplies opt, an in-memory synthetic dataset and
     stubs for the plotting imports; nothing of this repo is on that path.  Step time = spacing of consecutive
     iterations (first gradient-penalty draw of each, esrgan.py:598), median over the timed steps."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import ref_harness
-    torch.set_num_threads(os.cpu_count() or 1)
-    res = ref_harness.run(os.path.join(ROOT, "baseline", "_ref"), None, n_batches=warmup + steps + 1, batch_size=batch,
-                          seed=4321, factor=cfg["factor"], residual_blocks=cfg["nb"], preload=True)
+    import tempfile
+    out = os.path.join(tempfile.mkdtemp(prefix="srb_refarm_"), "trace.json")
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")     # esrgan.py:173 takes cuda:0 when it sees one: this arm is the CPU path
+    cmd = [sys.executable, os.path.join(ROOT, "tests", "ref_harness.py"), "--ref", os.path.join(ROOT, "baseline", "_ref"),
+           "--out", out, "--n-batches", str(warmup + steps + 1), "--batch-size", str(batch), "--seed", "4321",
+           "--factor", str(cfg["factor"]), "--residual-blocks", str(cfg["nb"]), "--preload",
+           "--threads", str(os.cpu_count() or 1)]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=1500)
+    if r.returncode != 0:
+        raise RuntimeError("reference run failed: " + r.stderr[-300:])
+    res = json.load(open(out))
+    if res.get("device") != "cpu":
+        raise RuntimeError("reference run did not stay on the CPU")
     t = res["step_t"]
     d = sorted(b - a for a, b in zip(t[warmup:-1], t[warmup + 1:]))
     dt = d[len(d) // 2]

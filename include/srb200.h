@@ -262,9 +262,20 @@ int srb_extract_batch(const float* pairs, int B, int N, int etaBins, int phiBins
 /* ---- evaluation post-processing (csrc/eval_stats.cu) ----------------------------------
  * srb_image_stats: evaluation/eval.py:323-335 (collector modes max, min, mean, nnz, sum, meannnz) and eval.py:98-105
  * (get_nth_hardest, n = 1..nmax <= 8) for a batch in one pass.
- *   img : fp32 [B][HW];  out : fp32 [B][6 + nmax] = { max, min, mean, count(> thres), sum, mean of pixels > thres or 0,
- *   1st .. nmax-th largest pixel (duplicates counted) } */
+ *   img : fp32 [B][HW];  out : fp32 [B][7 + nmax] = { max, min, mean, count(> thres), sum, mean of pixels > thres or 0,
+ *   has-NaN flag (eval.py:319-321 skips such batches), 1st .. nmax-th largest pixel (duplicates counted) }, nmax <= 32
+ *   (options/default.json's eval_modes reach E_30) */
 int srb_image_stats(const float* img, int B, int HW, float thres, int nmax, float* out, void* stream);
+/* calculate_metrics, evaluation/eval.py:477-485, one batch: out[b] = { mean |SumPool_factor(gen) - lr|, mean |gen - hr| }. */
+int srb_l1_metrics(const float* gen, const float* hr, const float* lr, int B, int H, int W, int factor, float* out,
+                   void* stream);
+/* One image stack [B][H][W] added to running evaluation rasters (fp64, caller-owned, either may be NULL):
+ *   raster[f][f]   += number of pixels > thr_raster per position inside the factor x factor cells  (SumRaster.add,
+ *                     utils.py:290-293, evaluation mode 'hitogram')
+ *   mean_acc[H][W] += energy ? (sum_b max(pixel, thr_mean)) * (count_b pixel > thr_mean) : count_b pixel > thr_mean
+ *                     (MeanImage.add, utils.py:317-322, evaluation mode 'meanimg') */
+int srb_eval_rasters(const float* img, int B, int H, int W, int factor, float thr_raster, float thr_mean, int energy,
+                     double* raster, double* mean_acc, void* stream);
 
 /* Timing experiment aid: clock64 stamps of CTA 0's pipeline when srb_conv3x3 ran with flags bit 4 (tools/exp_conv.py). */
 int srb_igemm_read_stamps(long long* out16);

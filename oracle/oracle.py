@@ -205,6 +205,27 @@ def image_stats_numpy(Ln: np.ndarray, thres: float):
             "nnz": (Ln > thres).sum((1, 2, 3)), "sum": Ln.sum((1, 2, 3)), "meannnz": np.asarray(meannnz)}
 
 
+def sum_raster_numpy(imgs: np.ndarray, factor: int, threshold: float) -> np.ndarray:
+    """What one SumRaster.add call adds for one image stack (utils.py:290-293): the number of pixels above the threshold
+    at every position inside the factor x factor cells, summed over cells, channels and images."""
+    B, C, H, W = imgs.shape
+    cells = imgs.reshape(B, C, H // factor, factor, W // factor, factor)
+    return (cells > threshold).sum((0, 1, 2, 4)).astype(np.float64)
+
+
+def mean_image_numpy(imgs: np.ndarray, threshold: float, energy: bool) -> np.ndarray:
+    """What one MeanImage.add call adds for one image stack [B,1,H,W] (utils.py:317-322)."""
+    if energy or threshold <= 0:
+        return (np.clip(imgs, threshold, None).sum((0, 1)) * (imgs > threshold).sum((0, 1))).astype(np.float64)
+    return (imgs > threshold).sum((0, 1)).astype(np.float64)
+
+
+def l1_metrics_numpy(gen_hr: Tensor, hr: Tensor, lr: Tensor, factor: int) -> Tuple[np.ndarray, np.ndarray]:
+    """calculate_metrics, evaluation/eval.py:477-485: per-image (lr L1, hr L1)."""
+    gen_lr = sum_pool(gen_hr, factor)
+    return ((gen_lr - lr).abs().numpy().mean((1, 2, 3)), (gen_hr - hr).abs().numpy().mean((1, 2, 3)))
+
+
 # ----------------------------------------------------------------------------
 # losses (esrgan.py:457-626), default-active terms only
 # ----------------------------------------------------------------------------

@@ -240,7 +240,10 @@ conv3x3_chain_kernel(const __grid_constant__ ChainParams cp) {
               for (int i = 0; i < 32; ++i) v[i] += __uint_as_float(acc[i]);
             }
           }
-          if (valid) igemm_store_row<true>(p, v, q, py, px, nt, half);
+          if (valid) {
+            if (p.ext) igemm_store_row<true, true>(p, v, q, py, px, nt, half);
+            else igemm_store_row<true, false>(p, v, q, py, px, nt, half);
+          }
           if (p.colsum && valid) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) vs[i] += v[i];

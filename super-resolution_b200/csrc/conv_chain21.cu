@@ -223,7 +223,7 @@ conv3x3_chain21_kernel(const __grid_constant__ ChainParams cp) {
             for (int i = 0; i < 32; ++i) v[i] += __uint_as_float(d0[i]);
           }
           par ^= 1;
-          if (valid) igemm_store_row<true>(p, v, q, py, px, nt, half);
+          if (valid) igemm_store_row<true, true>(p, v, q, py, px, nt, half);
           if (p.colsum && valid) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) vs[i] += v[i];

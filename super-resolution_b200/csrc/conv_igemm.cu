@@ -60,6 +60,7 @@ struct IgemmParams {
   float* y32; int y32_cstride, y32_coff;                    // optional fp32 copy of the output (plain store)
   const __nv_bfloat16* res3; int res3_cstride, res3_coff; float res3_scale;
   const float* chan_scale;                                  // optional [batch][cout] factor on (acc + bias)
+  int ext;                                                  // any of the four fields above in use (EXT epilogue)
   int base_offset_mode;
   int dbg;          // timing experiments only (flags >> 1): 1 no weight reloads, 2 no activation reloads, 4 no epilogue I/O
 };
@@ -158,7 +159,10 @@ __device__ __forceinline__ void add_residual32(float (&v)[32], const void* base,
   }
 }
 
-template <bool COHERENT = false>
+// EXT = false is the round-1 epilogue (bf16 residuals only); EXT = true adds the fp32 residual streams, the third
+// residual, the per-image channel factor and the fp32 output copy.  Two instantiations so that the common layers (four
+// of the five convolutions of a dense block) keep the lean code: the K = 64 / 128 layers are epilogue-bound.
+template <bool COHERENT = false, bool EXT = false>
 __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)[32], int q, int py, int px, int nt,
                                                 int half) {
   const int n0 = nt * 64;
@@ -184,7 +188,7 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
       v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
     }
   }
-  if (p.chan_scale) {
+  if (EXT && p.chan_scale) {
     const float4* cs4 = reinterpret_cast<const float4*>(p.chan_scale + static_cast<size_t>(q / p.P) * p.cout + c0);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -195,11 +199,11 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] *= p.alpha;
   if (p.res1) add_residual32<COHERENT>(v, p.res1, static_cast<size_t>(q), p.res1_cstride, p.res1_coff, c0, p.res1_scale,
-                                       p.res_f32 & 1);
+                                       EXT && (p.res_f32 & 1));
   if (p.res2) add_residual32<COHERENT>(v, p.res2, static_cast<size_t>(q), p.res2_cstride, p.res2_coff, c0, p.res2_scale,
-                                       p.res_f32 & 2);
-  if (p.res3) add_residual32<COHERENT>(v, p.res3, static_cast<size_t>(q), p.res3_cstride, p.res3_coff, c0, p.res3_scale,
-                                       false);
+                                       EXT && (p.res_f32 & 2));
+  if (EXT && p.res3) add_residual32<COHERENT>(v, p.res3, static_cast<size_t>(q), p.res3_cstride, p.res3_coff, c0,
+                                              p.res3_scale, false);
   if (p.act == SRB_ACT_LRELU) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.slope;
@@ -228,7 +232,7 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
     for (int i = 0; i < 32; ++i) bits |= (v[i] > 0.f ? 1u : 0u) << i;
     p.sign_out[static_cast<size_t>(q) * p.sign_cstride + p.sign_coff + (c0 >> 5)] = bits;
   }
-  if (p.y32) {
+  if (EXT && p.y32) {
     float4* y4 = reinterpret_cast<float4*>(p.y32 + static_cast<size_t>(q) * p.y32_cstride + p.y32_coff + c0);
 #pragma unroll
     for (int i = 0; i < 8; ++i) y4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
@@ -416,7 +420,10 @@ conv3x3_igemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_co
             for (int i = 0; i < 32; ++i) v[i] += __uint_as_float(acc[i]);
           }
         }
-        if (valid) igemm_store_row(p, v, q, py, px, nt, half);
+        if (valid) {
+          if (p.ext) igemm_store_row<false, true>(p, v, q, py, px, nt, half);
+          else igemm_store_row<false, false>(p, v, q, py, px, nt, half);
+        }
         if (p.colsum && valid) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) vs[i] += v[i];
@@ -550,6 +557,7 @@ int igemm_fill(const srb_conv3x3_args* a, const IgemmPlan& pl, IgemmParams* pp, 
   p.y32 = a->y32; p.y32_cstride = a->y32_cstride; p.y32_coff = a->y32_coff;
   p.res3 = (const __nv_bfloat16*)a->res3; p.res3_cstride = a->res3_cstride; p.res3_coff = a->res3_coff; p.res3_scale = a->res3_scale;
   p.chan_scale = a->chan_scale;
+  p.ext = (p.res_f32 || p.y32 || p.res3 || p.chan_scale) ? 1 : 0;
   if ((p.y32 || p.chan_scale) && a->store_mode != SRB_STORE_PLAIN)
     return set_error("conv3x3: y32 / chan_scale need a plain store");
   if (p.y32 && ((a->y32_cstride | a->y32_coff) % 4)) return set_error("conv3x3: y32 stride / offset must keep 16-byte alignment");

@@ -198,9 +198,15 @@ def main():
     ap.add_argument("--residual-blocks", type=int, default=10)
     ap.add_argument("--overrides", default="{}")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--preload", action="store_true")
+    ap.add_argument("--threads", type=int, default=0)
     a = ap.parse_args()
+    if a.threads:
+        import torch
+        torch.set_num_threads(a.threads)
     res = run(a.ref, a.models, n_batches=a.n_batches, batch_size=a.batch_size, seed=a.seed, factor=a.factor,
-              residual_blocks=a.residual_blocks, overrides=json.loads(a.overrides), quiet=not a.verbose)
+              residual_blocks=a.residual_blocks, overrides=json.loads(a.overrides), quiet=not a.verbose,
+              preload=a.preload)
     with open(a.out, "w") as f:
         json.dump(res, f)
     print("wrote", a.out, {k: v[-1] for k, v in res["loss"].items() if v and k in ("g_loss", "d_loss_def", "d_loss_pow")})

@@ -10,7 +10,7 @@ from srb200.train_step import GANTrainStep
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 dev = torch.device("cuda:0")
-G, Ds = bench.build_models(dev)
+G, Ds = bench.build_models(dev, bench.CONFIGS['gan'])
 tr = GANTrainStep(G, Ds, factor=4)
 hr, lr = O.synthetic_jets(B, 80, 4, 1)
 hr, lr = hr.to(dev), lr.to(dev)
