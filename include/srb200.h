@@ -185,6 +185,11 @@ int srb_conv_out_bwd(const float* z, const float* g_out, const float* g_srs, int
                      int gy_coff, float* dw, float* db, void* stream);
 int srb_unshuffle2(const void* src, int s_cstride, int s_coff, int B, int H, int W, int C, void* dst, int d_cstride,
                    int d_coff, void* stream);
+/* Dropout2d backward (models.py:29-31,39-40 under autograd): x = C-channel slot of a PNHWC bf16 buffer holding the
+ * gradient w.r.t. a DenseResidualBlock's output; copy <- x (for the identity paths), x <- x * mask[image][channel]
+ * in place (what the fifth convolution's weight / input gradients see).  mask: fp32 [B][C] (0 or 1/(1-p)). */
+int srb_chan_mask_split(void* x, int x_cstride, int x_coff, void* copy, int c_cstride, int c_coff, const float* mask,
+                        int B, int H, int W, int C, void* stream);
 
 /* ---- discriminator stack and SumPool2d (csrc/disc.cu), fp32 NCHW ---------------------------------
  * srb_dconv_fwd/dgrad/wgrad: nn.Conv2d(k=3, padding=1, stride 1|2) of discriminator_block (models.py:140-146,168)
@@ -244,6 +249,11 @@ int srb_adam_step(float* p, const float* g, float* m, float* v, long long n, flo
                   void* stream);
 int srb_pixel_losses(const float* gen, const float* gt, const float* lr, int B, int H, int W, int k, float w_hr,
                      float w_lr, int accumulate, float* msign, float* dsign, float* acc, float* grad, void* stream);
+/* The same with the low-resolution term taken on powered images (opt.scaling_power != 1, esrgan.py:472-473,490 for the
+ * "pow" branch): loss_lr = L1(SumPool(gen)^lr_power, lr^lr_power), gradient through torch.pow's derivative. */
+int srb_pixel_losses_pow(const float* gen, const float* gt, const float* lr, int B, int H, int W, int k, float w_hr,
+                         float w_lr, float lr_power, int accumulate, float* msign, float* dsign, float* acc,
+                         float* grad, void* stream);
 int srb_ragan(const float* u, const float* v, int B, int n, float eps, float* loss, float* gu, float* gv,
               void* stream);
 int srb_gp_fwd(const float* g, int B, int n, float coef, float* norms, float* loss, void* stream);

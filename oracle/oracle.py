@@ -60,9 +60,31 @@ def conv3x3_numpy(x: np.ndarray, w: np.ndarray, b: Optional[np.ndarray], stride:
 # ----------------------------------------------------------------------------
 # generator (models.py:9-135)
 # ----------------------------------------------------------------------------
-def dense_residual_block(sd: SD, prefix: str, x: Tensor) -> Tensor:
+class DropMasks:
+    """Dropout2d channel masks of the dense blocks (models.py:29-31,39-40), in forward order.  nn.Dropout2d draws
+    ``empty(B, C, 1, 1).bernoulli_(1 - p) / (1 - p)`` from the default generator per call; drawing the same way in the
+    same order under the same seed reproduces the reference's masks on the CPU.  ``masks`` keeps what was drawn (or is
+    preset) so the device path can be fed exactly the same factors."""
+
+    def __init__(self, drop_rate: float, masks: Optional[List[Tensor]] = None):
+        self.p = float(drop_rate)
+        self.masks: List[Tensor] = [] if masks is None else list(masks)
+        self.preset = masks is not None
+        self.i = 0
+
+    def next(self, like: Tensor) -> Tensor:
+        if self.preset:
+            m = self.masks[self.i]
+        else:
+            m = torch.empty(like.shape[0], like.shape[1], 1, 1).bernoulli_(1 - self.p).div_(1 - self.p)
+            self.masks.append(m)
+        self.i += 1
+        return m
+
+
+def dense_residual_block(sd: SD, prefix: str, x: Tensor, drop: Optional[DropMasks] = None) -> Tensor:
     """models.py:34-41.  conv k sees concat(x, out_1..out_{k-1}); LeakyReLU(0.01)
-    after convs 1-4; returns out5 * 0.2 + x."""
+    after convs 1-4; Dropout2d on out5 in training when drop_rate > 0; returns out5 * 0.2 + x."""
     inputs = x
     out = x
     for k in range(1, 6):
@@ -70,14 +92,16 @@ def dense_residual_block(sd: SD, prefix: str, x: Tensor) -> Tensor:
         if k < 5:
             out = F.leaky_relu(out, G_LRELU_SLOPE)
         inputs = torch.cat([inputs, out], 1)
+    if drop is not None:
+        out = out * drop.next(out)                                           # models.py:39-40
     return out * DRB_RES_SCALE + x
 
 
-def rrdb(sd: SD, prefix: str, x: Tensor, res_scale: float) -> Tensor:
+def rrdb(sd: SD, prefix: str, x: Tensor, res_scale: float, drop: Optional[DropMasks] = None) -> Tensor:
     """models.py:44-53: three dense blocks, then * res_scale + x."""
     out = x
     for j in range(3):
-        out = dense_residual_block(sd, f"{prefix}dense_blocks.{j}.", out)
+        out = dense_residual_block(sd, f"{prefix}dense_blocks.{j}.", out, drop)
     return out * res_scale + x
 
 
@@ -89,25 +113,40 @@ def _count(sd: SD, pattern: str) -> int:
 
 
 def generator_forward(sd: SD, x: Tensor, *, res_scale: float = 0.2, thres: float = 0.0,
-                      training: bool = True) -> Tuple[Tensor, Tensor]:
-    """GeneratorRRDB.forward, models.py:120-135 (default upsampling variant,
-    models.py:85-91; no final res blocks).  Returns (output, srs)."""
+                      training: bool = True, drop: Optional[DropMasks] = None) -> Tuple[Tensor, Tensor]:
+    """GeneratorRRDB.forward, models.py:120-135, every constructor variant: upsampling stages are recognised by their
+    weight shape ([4F,F,3,3]: conv + LeakyReLU + PixelShuffle, models.py:85-91; [F,F,2,2]: ConvTranspose2d(k=2, s=2) +
+    LeakyReLU, models.py:70-83), ``res_blocks_final.*`` entries are the num_final_layer_res blocks (models.py:93-94,
+    128-130), ``drop`` carries the Dropout2d masks (training only).  Returns (output, srs)."""
     power = float(sd["power"].item())
     multiplier = float(sd["multiplier"].item())
     nb = _count(sd, "res_blocks.%d.")
+    nfinal = _count(sd, "res_blocks_final.%d.")
     up_idx = sorted({int(k.split(".")[1]) for k in sd if k.startswith("upsampling.") and k.endswith("weight")})
+    if not training:
+        drop = None
 
     x = multiplier * (x ** power)                                            # models.py:122
     out1 = F.conv2d(x, sd["conv1.weight"], sd["conv1.bias"], 1, 1)           # 123
     out = out1
     for i in range(nb):                                                      # 124
-        out = rrdb(sd, f"res_blocks.{i}.", out, res_scale)
+        out = rrdb(sd, f"res_blocks.{i}.", out, res_scale, drop)
     out2 = F.conv2d(out, sd["conv2.weight"], sd["conv2.bias"], 1, 1)         # 125
     out = out1 + out2                                                        # 126
-    for i in up_idx:                                                         # 127 / 85-91
-        out = F.conv2d(out, sd[f"upsampling.{i}.weight"], sd[f"upsampling.{i}.bias"], 1, 1)
-        out = F.leaky_relu(out, G_LRELU_SLOPE)
-        out = F.pixel_shuffle(out, 2)
+    for i in up_idx:                                                         # 127 / 70-91
+        w = sd[f"upsampling.{i}.weight"]
+        if w.shape[-1] == 2:
+            out = F.conv_transpose2d(out, w, sd[f"upsampling.{i}.bias"], stride=2)
+            out = F.leaky_relu(out, G_LRELU_SLOPE)
+        else:
+            out = F.conv2d(out, w, sd[f"upsampling.{i}.bias"], 1, 1)
+            out = F.leaky_relu(out, G_LRELU_SLOPE)
+            out = F.pixel_shuffle(out, 2)
+    if nfinal:                                                               # 128-130
+        out3 = out
+        for i in range(nfinal):
+            out3 = rrdb(sd, f"res_blocks_final.{i}.", out3, res_scale, drop)
+        out = out3 + out
     out = F.conv2d(out, sd["conv3.0.weight"], sd["conv3.0.bias"], 1, 1)      # 131 / 96-100
     out = F.leaky_relu(out, G_LRELU_SLOPE)
     out = F.conv2d(out, sd["conv3.2.weight"], sd["conv3.2.bias"], 1, 1) / multiplier
@@ -347,7 +386,18 @@ def seeded_state_dict(shapes: Dict[str, Tuple[int, ...]], seed: int, gain: float
     return sd
 
 
-def generator_shapes(channels=1, filters=64, num_res_blocks=10, num_upsample=2) -> Dict[str, Tuple[int, ...]]:
+def upsampling_kinds(num_upsample: int, use_transposed_conv=False, fully_tconv_upsample=False) -> List[str]:
+    """'ps' (conv + LeakyReLU + PixelShuffle) or 'tconv' (ConvTranspose2d + LeakyReLU) per stage, models.py:70-91:
+    use_transposed_conv is tested first and alternates ps / tconv."""
+    if use_transposed_conv:
+        return ["ps" if i % 2 == 0 else "tconv" for i in range(num_upsample)]
+    if fully_tconv_upsample:
+        return ["tconv"] * num_upsample
+    return ["ps"] * num_upsample
+
+
+def generator_shapes(channels=1, filters=64, num_res_blocks=10, num_upsample=2, use_transposed_conv=False,
+                     fully_tconv_upsample=False, num_final_layer_res=0) -> Dict[str, Tuple[int, ...]]:
     """state_dict names/shapes of GeneratorRRDB in registration order (models.py:58-103;
     SURVEY.md section 5 'Checkpoint')."""
     s: Dict[str, Tuple[int, ...]] = {"power": (1,), "multiplier": (1,)}
@@ -359,8 +409,19 @@ def generator_shapes(channels=1, filters=64, num_res_blocks=10, num_upsample=2) 
                 p = f"res_blocks.{i}.dense_blocks.{j}.b{k}.0."
                 s[p + "weight"] = (F_, k * F_, 3, 3); s[p + "bias"] = (F_,)
     s["conv2.weight"] = (F_, F_, 3, 3); s["conv2.bias"] = (F_,)
-    for u in range(num_upsample):
-        s[f"upsampling.{3 * u}.weight"] = (4 * F_, F_, 3, 3); s[f"upsampling.{3 * u}.bias"] = (4 * F_,)
+    idx = 0
+    for kind in upsampling_kinds(num_upsample, use_transposed_conv, fully_tconv_upsample):
+        if kind == "ps":
+            s[f"upsampling.{idx}.weight"] = (4 * F_, F_, 3, 3); s[f"upsampling.{idx}.bias"] = (4 * F_,)
+            idx += 3
+        else:
+            s[f"upsampling.{idx}.weight"] = (F_, F_, 2, 2); s[f"upsampling.{idx}.bias"] = (F_,)
+            idx += 2
+    for i in range(num_final_layer_res):
+        for j in range(3):
+            for k in range(1, 6):
+                p = f"res_blocks_final.{i}.dense_blocks.{j}.b{k}.0."
+                s[p + "weight"] = (F_, k * F_, 3, 3); s[p + "bias"] = (F_,)
     s["conv3.0.weight"] = (F_, F_, 3, 3); s["conv3.0.bias"] = (F_,)
     s["conv3.2.weight"] = (channels, F_, 3, 3); s["conv3.2.bias"] = (channels,)
     return s
@@ -379,8 +440,10 @@ def discriminator_shapes(in_channels=1, channels=(16, 32, 32, 64)) -> Dict[str, 
 
 
 def make_generator_sd(seed: int, *, channels=1, filters=64, num_res_blocks=10, num_upsample=2,
-                      power=1.0, multiplier=1.0, gain=1.0) -> SD:
-    shapes = generator_shapes(channels, filters, num_res_blocks, num_upsample)
+                      power=1.0, multiplier=1.0, gain=1.0, use_transposed_conv=False, fully_tconv_upsample=False,
+                      num_final_layer_res=0) -> SD:
+    shapes = generator_shapes(channels, filters, num_res_blocks, num_upsample, use_transposed_conv,
+                              fully_tconv_upsample, num_final_layer_res)
     sd = {"power": torch.tensor([float(power)]), "multiplier": torch.tensor([float(multiplier)])}
     sd.update(seeded_state_dict(shapes, seed, gain))
     return {k: sd[k] for k in shapes}

@@ -19,8 +19,12 @@
 //   neighbours' layer l-1, which is after every earlier read of those rows.
 //   Residual / mask rows are read by the thread that wrote them (same tile -> same CTA -> same warp/lane) with
 //   ld.global.cg, never through the non-coherent path.
-// All CTAs of the grid must be co-resident (grid <= SM count, one CTA per SM by shared-memory footprint), which the
-// launch guarantees; a flag wait that never completes records a fault word and traps (no hung GPU).
+// Progress.  grid <= SM count and one CTA per SM by shared-memory footprint, so every CTA gets an SM of its own as soon
+// as nothing else holds it.  While another stream's kernel occupies SMs (NCCL channel CTAs of the bucketed all-reduce,
+// the discriminator streams) some CTAs start late; their neighbours spin in chain_wait_flag until they arrive.  That is
+// a delay, not a deadlock: a waiting CTA only ever waits for tiles of the PREVIOUS layer, foreign kernels never wait for
+// this one, and a late CTA needs no SM a spinning CTA holds.  The spin limit (2^26 polls of >= 40 ns, several seconds)
+// exists only so that a protocol bug surfaces as a fault word + trap instead of a hung GPU.
 //
 // Everything else (operand staging, four MMA issuers with private TMEM accumulators, epilogue) is conv_igemm.cu's.
 #include "common.cuh"
@@ -51,7 +55,7 @@ __device__ __forceinline__ void chain_wait_flag(const int* f, int target, int la
   uint32_t spins = 0;
   while (ld_acquire_gpu(f) < target) {
     __nanosleep(40);
-    if (++spins > (1u << 21)) {
+    if (++spins > (1u << 26)) {
       atomicExch(&g_srb_fault, 0xC0000000u | (static_cast<uint32_t>(layer & 0xff) << 16) | (blockIdx.x & 0xffffu));
       __trap();
     }

@@ -302,6 +302,36 @@ __global__ void unshuffle_kernel(const __nv_bfloat16* __restrict__ src, int s_cs
       *reinterpret_cast<const uint4*>(src + srow * s_cstride + s_coff + g * 8);
 }
 
+// ---------------------------------------------------------------- Dropout2d backward helper
+// x: PNHWC slot of C channels (the gradient w.r.t. a dense block's output).  copy <- x (unmasked, for the identity
+// paths), x <- x * m[image][channel] in place (what the fifth convolution's gradients see, models.py:39-40).
+// One thread = 8 channels of one valid pixel.
+__global__ void chan_mask_split_kernel(__nv_bfloat16* __restrict__ x, int x_cstride, int x_coff,
+                                       __nv_bfloat16* __restrict__ copy, int c_cstride, int c_coff,
+                                       const float* __restrict__ m, int B, int H, int W, int Cc) {
+  const int groups = Cc / 8;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long total = 1LL * B * H * W * groups;
+  if (idx >= total) return;
+  const int g = int(idx % groups);
+  long long r = idx / groups;
+  const int px = int(r % W); r /= W;
+  const int py = int(r % H);
+  const int b = int(r / H);
+  const size_t row = (static_cast<size_t>(b) * (H + 1) + py) * (W + 1) + px;
+  uint4* xp = reinterpret_cast<uint4*>(x + row * x_cstride + x_coff + g * 8);
+  const uint4 v = *xp;
+  *reinterpret_cast<uint4*>(copy + row * c_cstride + c_coff + g * 8) = v;
+  const float4 m0 = __ldg(reinterpret_cast<const float4*>(m + static_cast<size_t>(b) * Cc + g * 8));
+  const float4 m1 = __ldg(reinterpret_cast<const float4*>(m + static_cast<size_t>(b) * Cc + g * 8) + 1);
+  uint4 o;
+  o.x = pack_bf16(bf16lo(v.x) * m0.x, bf16hi(v.x) * m0.y);
+  o.y = pack_bf16(bf16lo(v.y) * m0.z, bf16hi(v.y) * m0.w);
+  o.z = pack_bf16(bf16lo(v.z) * m1.x, bf16hi(v.z) * m1.y);
+  o.w = pack_bf16(bf16lo(v.w) * m1.z, bf16hi(v.w) * m1.w);
+  *xp = o;
+}
+
 }  // namespace srb
 
 // ================================================================== C ABI
@@ -454,5 +484,17 @@ extern "C" int srb_unshuffle2(const void* src, int s_cstride, int s_coff, int B,
   unshuffle_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)src, s_cstride, s_coff, B, H, W, C, (__nv_bfloat16*)dst, d_cstride, d_coff);
   SRB_LAUNCH_CHECK("unshuffle");
+  return 0;
+}
+
+extern "C" int srb_chan_mask_split(void* x, int x_cstride, int x_coff, void* copy, int c_cstride, int c_coff,
+                                   const float* mask, int B, int H, int W, int C, void* stream) {
+  if (!x || !copy || !mask) return set_error("chan_mask_split: null pointer");
+  if (C % 8 || x_cstride % 8 || c_cstride % 8 || x_coff % 8 || c_coff % 8)
+    return set_error("chan_mask_split: channels / strides / offsets must be multiples of 8");
+  const long long total = 1LL * B * H * W * (C / 8);
+  chan_mask_split_kernel<<<ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      (__nv_bfloat16*)x, x_cstride, x_coff, (__nv_bfloat16*)copy, c_cstride, c_coff, mask, B, H, W, C);
+  SRB_LAUNCH_CHECK("chan_mask_split");
   return 0;
 }

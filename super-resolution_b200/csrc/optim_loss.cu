@@ -98,8 +98,10 @@ __global__ void pix_mean_kernel(const float* __restrict__ gen, const float* __re
   if (threadIdx.x == 0) atomicAdd(acc, a);
 }
 // B: per LR pixel, d = sum of k x k block of gen - lr; sign to dsign; sum |d| into acc[1]
+// lr_power != 1 (opt.scaling_power, esrgan.py:472-473,490 for k = 1): d = pool^p - lr^p and dsign carries the whole
+// derivative factor sign(d) * p * pool^(p-1) (torch.pow semantics, including its infinities at pool == 0 for p < 1).
 __global__ void pix_lr_kernel(const float* __restrict__ gen, const float* __restrict__ lr, int B, int H, int W, int k,
-                              float* __restrict__ dsign, float* __restrict__ acc) {
+                              float lr_power, float* __restrict__ dsign, float* __restrict__ acc) {
   const int h = H / k, w = W / k;
   const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   float a = 0.f;
@@ -109,8 +111,14 @@ __global__ void pix_lr_kernel(const float* __restrict__ gen, const float* __rest
     float s = 0.f;
     for (int r = 0; r < k; ++r)
       for (int c = 0; c < k; ++c) s += g[r * W + c];
-    s -= lr[i];
-    dsign[i] = s > 0.f ? 1.f : (s < 0.f ? -1.f : 0.f);
+    float dfac = 1.f;
+    if (lr_power != 1.f) {
+      dfac = lr_power * powf(s, lr_power - 1.f);
+      s = powf(s, lr_power) - powf(lr[i], lr_power);
+    } else {
+      s -= lr[i];
+    }
+    dsign[i] = (s > 0.f ? 1.f : (s < 0.f ? -1.f : 0.f)) * dfac;
     a = fabsf(s);
   }
   a = block_sum(a);
@@ -268,12 +276,18 @@ extern "C" int srb_adam_step(float* p, const float* g, float* m, float* v, long 
 extern "C" int srb_pixel_losses(const float* gen, const float* gt, const float* lr, int B, int H, int W, int k,
                                 float w_hr, float w_lr, int accumulate, float* msign, float* dsign, float* acc,
                                 float* grad, void* stream) {
+  return srb_pixel_losses_pow(gen, gt, lr, B, H, W, k, w_hr, w_lr, 1.f, accumulate, msign, dsign, acc, grad, stream);
+}
+
+extern "C" int srb_pixel_losses_pow(const float* gen, const float* gt, const float* lr, int B, int H, int W, int k,
+                                    float w_hr, float w_lr, float lr_power, int accumulate, float* msign, float* dsign,
+                                    float* acc, float* grad, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   const int HW = H * W, h = H / k, w = W / k;
   cudaMemsetAsync(acc, 0, 2 * sizeof(float), st);
   pix_mean_kernel<<<ceil_div(HW, 256), 256, 0, st>>>(gen, gt, B, HW, msign, acc);
   SRB_CHK("pix_mean");
-  pix_lr_kernel<<<ceil_div(1LL * B * h * w, 256), 256, 0, st>>>(gen, lr, B, H, W, k, dsign, acc);
+  pix_lr_kernel<<<ceil_div(1LL * B * h * w, 256), 256, 0, st>>>(gen, lr, B, H, W, k, lr_power, dsign, acc);
   SRB_CHK("pix_lr");
   if (grad) {
     pix_grad_kernel<<<ceil_div(1LL * B * HW, 256), 256, 0, st>>>(msign, dsign, B, H, W, k, w_hr / (float(B) * HW),

@@ -68,7 +68,8 @@ class _GeneratorFn(torch.autograd.Function):
         # grad mode is always off inside Function.forward, so the caller decides whether to keep activations
         ctx.gen = gen
         out, srs = gen._engine().forward(x, power=gen._host_scalar("power"), multiplier=gen._host_scalar("multiplier"),
-                                         thres=float(gen.thres), training=gen.training, save_for_backward=need)
+                                         thres=float(gen.thres), training=gen.training, save_for_backward=need,
+                                         drop_masks=gen._drop_masks)
         ctx.n = len(params)
         ctx.fwd_gen = gen._engine()._fwd_gen if need else None
         return out, srs
@@ -117,9 +118,11 @@ class GeneratorRRDB(nn.Module):
         self.thres = 0
         self.power = nn.Parameter(torch.Tensor([power]), False)
         self.multiplier = nn.Parameter(torch.Tensor([multiplier]), False)
+        stages = [("tconv" if isinstance(m, nn.ConvTranspose2d) else "ps", "upsampling.%d" % i)
+                  for i, m in enumerate(self.upsampling) if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d))]
         self._cfg = dict(channels=channels, filters=filters, num_res_blocks=num_res_blocks, num_upsample=num_upsample,
-                         res_scale=res_scale)
-        self._native = not (use_transposed_conv or fully_tconv_upsample or num_final_layer_res > 0 or drop_rate > 0)
+                         res_scale=res_scale, up_stages=stages, num_final=num_final_layer_res, drop_rate=drop_rate)
+        self._drop_masks = None      # tests: explicit Dropout2d factors {"main": [...], "final": [...]} for the next forwards
         self._eng = None
         self._scalars = {}
         if uniform_init:
@@ -156,9 +159,6 @@ class GeneratorRRDB(nn.Module):
         return F.hardshrink(F.relu(x), lambd=self.thres ** pow.item())
 
     def forward(self, x):
-        if not self._native:
-            raise RuntimeError("CUDA srb200: use_transposed_conv / fully_tconv_upsample / num_final_layer_res / "
-                               "drop_rate variants are constructor-surface only in this build (SURVEY.md 8f-4)")
         params = list(self.parameters())
         need = torch.is_grad_enabled() and any(p.requires_grad for p in params)
         out, srs = _GeneratorFn.apply(self, need, x, *params)

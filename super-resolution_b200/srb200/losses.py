@@ -26,17 +26,18 @@ class PixelLossWork:
         self.acc = torch.zeros(2, device=dev)
 
 
-def pixel_losses(gen, gt, lr, k, w_hr, w_lr, grad_out, accumulate, work: PixelLossWork):
-    """loss_hr = L1(mean_b gen, mean_b gt) (esrgan.py:487); loss_lr = L1(SumPool_k(gen), lr) (471,490).
+def pixel_losses(gen, gt, lr, k, w_hr, w_lr, grad_out, accumulate, work: PixelLossWork, lr_power: float = 1.0):
+    """loss_hr = L1(mean_b gen, mean_b gt) (esrgan.py:487); loss_lr = L1(SumPool_k(gen), lr) (471,490), or with
+    ``lr_power`` p != 1 L1(SumPool_k(gen)^p, lr^p) (472-473: the scaling_power branch).
     Adds w_hr * d loss_hr/d gen + w_lr * d loss_lr/d gen into ``grad_out`` (or overwrites it).
     Returns (loss_hr, loss_lr) as 0-dim device tensors."""
     gen, gt, lr = _c(gen), _c(gt), _c(lr)
     B, Cc, H, W = gen.shape
     assert Cc == 1, "pixel loss kernel is single-channel (jet images)"
-    L.check(L.lib().srb_pixel_losses(gen.data_ptr(), gt.data_ptr(), lr.data_ptr(), B, H, W, k, float(w_hr),
-                                     float(w_lr), int(accumulate), work.msign.data_ptr(), work.dsign.data_ptr(),
-                                     work.acc.data_ptr(), grad_out.data_ptr() if grad_out is not None else None,
-                                     _st()), "pixel_losses")
+    L.check(L.lib().srb_pixel_losses_pow(gen.data_ptr(), gt.data_ptr(), lr.data_ptr(), B, H, W, k, float(w_hr),
+                                         float(w_lr), float(lr_power), int(accumulate), work.msign.data_ptr(),
+                                         work.dsign.data_ptr(), work.acc.data_ptr(),
+                                         grad_out.data_ptr() if grad_out is not None else None, _st()), "pixel_losses")
     acc = work.acc.clone()
     return acc[0] / (H * W), acc[1] / (B * (H // k) * (W // k))
 

@@ -14,10 +14,28 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
 import ref_harness  # noqa: E402
 
+VARIANTS = {      # small runs of the non-default training recipes the fused step also covers
+    "scaling_power_0.5": dict(scaling_power=0.5),                   # esrgan.py:470-473: the "pow" branch on x ** 0.5
+    "second_discriminators": dict(second_discr_reset_interval=4),   # esrgan.py:221-237,495-505,789-795
+}
+
 if __name__ == "__main__":
-    res = ref_harness.run("/root/reference", None, n_batches=20, batch_size=16, seed=4321, factor=4, residual_blocks=10)
-    res.pop("stdout_tail")
-    res["models_file"] = "reference models.py"
-    with open(os.path.join(HERE, "golden_trace_v1.json"), "w") as f:
-        json.dump(res, f)
-    print({k: (v[0], v[-1]) for k, v in res["loss"].items() if any(v)})
+    if "--variants" not in sys.argv:
+        res = ref_harness.run("/root/reference", None, n_batches=20, batch_size=16, seed=4321, factor=4, residual_blocks=10)
+        res.pop("stdout_tail")
+        res.pop("step_t", None)
+        res["models_file"] = "reference models.py"
+        with open(os.path.join(HERE, "golden_trace_v1.json"), "w") as f:
+            json.dump(res, f)
+        print({k: (v[0], v[-1]) for k, v in res["loss"].items() if any(v)})
+    out = {}
+    for name, ov in VARIANTS.items():
+        r = ref_harness.run("/root/reference", None, n_batches=6, batch_size=4, seed=977, factor=4, residual_blocks=1,
+                            overrides=ov)
+        r.pop("stdout_tail")
+        r.pop("step_t", None)
+        r["models_file"] = "reference models.py"
+        out[name] = r
+        print(name, {k: (v[0], v[-1]) for k, v in r["loss"].items() if any(v)})
+    with open(os.path.join(HERE, "golden_trace_variants_v1.json"), "w") as f:
+        json.dump(out, f)
