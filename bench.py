@@ -426,8 +426,10 @@ def run_ours(args):
     #      CUDA events around every launch on the launching stream
     pk = peaks()
     ops.PROFILE = []
+    d_streams, trainer.d_streams = trainer.d_streams, False     # kernels timed alone: no discriminator work beside them
     trainer.step(lr, hr)
     torch.cuda.synchronize()
+    trainer.d_streams = d_streams
     prof, ops.PROFILE = ops.PROFILE, None
     agg = {}
     for kind, fl, e0, e1 in prof:
@@ -574,7 +576,8 @@ def run_ours(args):
             "data": "synthetic sparse jet images (20-60 hits/image, Exp(5) energies), seeded weights",
             "config": {"workload": cfg["text"],
                        "per_gpu_batch": B, "global_batch": world * B, "parallelism": f"dp{world}",
-                       "launch": "eager" if args.no_graph else "one CUDA graph per step (C-ABI launches captured)",
+                       "launch": "eager" if args.no_graph else "one CUDA graph per step (C-ABI launches captured; the two "
+                                 "discriminators on their own streams = parallel graph branches)",
                        "l2": "per-step working set (activations + gradients, > 1 GB) exceeds the 126 MB L2",
                        "dp_semantics": "batch statistics of the losses (esrgan.py:487,501-508) are per rank, as DDP "
                                        "around the reference would compute them"},

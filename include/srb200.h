@@ -260,6 +260,27 @@ int srb_gp_fwd(const float* g, int B, int n, float coef, float* norms, float* lo
 int srb_gp_bwd(const float* g, const float* norms, int B, int n, float coef, const float* gloss, float* gg,
                void* stream);
 
+/* ---- optional generator loss terms (csrc/opt_losses.cu; lambda = 0 in options/default.json) --------------------
+ * Each returns the loss as a device scalar and adds w * d loss / d generated into `grad` (accumulate != 0) or overwrites it.
+ * srb_soft_hist / srb_kld_hist / srb_soft_hist_bwd: DiffableHistogram (models.py:308-342) of the entries > 0 and KLD_hist
+ *     (utils.py:90-113) as used at esrgan.py:538-545: hist[j] = sum_{x>0} sigmoid(sigma (x - c_j + d_j/2)) -
+ *     sigmoid(sigma (x - c_j - d_j/2)); kld: loss and dq = d loss / d (generated histogram); bwd: chain rule to pixels.
+ * srb_nnz_loss : esrgan.py:530-533  mse(sum softgreater(gen, 0, sigma), count(gt > 0)) per image (utils.py:259-261).
+ * srb_mask_loss: esrgan.py:534-537  L1(sigmoid(sigma gen), sigmoid(sigma gt)) (nnz_mask, utils.py:271-272).
+ * srb_hit_loss : esrgan.py:546-550  mse of get_hitogram (utils.py:264-268) of generated and ground truth.          */
+int srb_soft_hist(const float* x, long long n, const float* centers, const float* deltas, int nbins, float sigma,
+                  float* hist, void* stream);
+int srb_kld_hist(const float* q_hist, const float* p_hist, const float* binsizes, int nbins, float* loss, float* dq,
+                 void* stream);
+int srb_soft_hist_bwd(const float* x, long long n, const float* centers, const float* deltas, int nbins, float sigma,
+                      const float* dq, float w, int accumulate, float* grad, void* stream);
+int srb_nnz_loss(const float* gen, const float* gt, int B, int HW, float sigma, float w, int accumulate,
+                 float* per_image, float* loss, float* grad, void* stream);
+int srb_mask_loss(const float* gen, const float* gt, long long n, float sigma, float w, int accumulate, float* loss,
+                  float* grad, void* stream);
+int srb_hit_loss(const float* gen, const float* gt, int B, int H, int W, int factor, float thr, float sig, float w,
+                 int accumulate, float* work, float* loss, float* grad, void* stream);
+
 /* ---- data path (csrc/data_path.cu) ---------------------------------------------------
  * srb_extract_batch: datasets.py:136-145 (extract) + datasets.py:247-249 / models.py:297-305 (SumPool2d) for a batch.
  *   pairs : fp32 [B][N][2] = (flat index, energy) lists, zero padded (a zero energy ends a list)

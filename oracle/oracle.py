@@ -290,11 +290,48 @@ def ragan_loss_d(pred_real: Tensor, pred_fake: Tensor) -> Tensor:
     return (loss_real + loss_fake) / 2
 
 
+def softgreater(x: Tensor, val: float, sigma: float = 5000, delta: float = 0) -> Tensor:
+    """utils.py:259-261."""
+    return torch.sigmoid(sigma * (x - val + delta))
+
+
+def nnz_mask(x: Tensor, sigma: float = 5e4) -> Tensor:
+    """utils.py:271-272."""
+    return torch.sigmoid(sigma * x)
+
+
+def get_hitogram(t: Tensor, factor: int, threshold: float = .1, sig: float = 80) -> Tensor:
+    """utils.py:264-268 for sig > 0: mean soft hit indicator per position inside the factor x factor cells."""
+    B, C, H, W = t.shape
+    cells = t.reshape(B, C, H // factor, factor, W // factor, factor)
+    return torch.sigmoid(sig * (cells - threshold)).mean((0, 1, 2, 4))
+
+
+def diffable_histogram(x: Tensor, binedges: Tensor, sigma: float) -> Tensor:
+    """DiffableHistogram.forward (models.py:308-342) built from bin edges, not batchwise: [1, bins]."""
+    delta = binedges[1:] - binedges[:-1]
+    centers = binedges[:-1] + .5 * delta
+    d = x.reshape(1, 1, -1) - centers.reshape(1, -1, 1)
+    half = delta.reshape(1, -1, 1) / 2
+    return (torch.sigmoid(sigma * (d + half)) - torch.sigmoid(sigma * (d - half))).sum(2)
+
+
+def kld_hist(q_entries: Tensor, p_entries: Tensor, binedges: Tensor) -> Tensor:
+    """KLD_hist.forward, utils.py:103-113 (q = generated histogram, p = ground-truth histogram)."""
+    binsizes = (binedges[1:] - binedges[:-1]).float()
+    n_p, n_q = p_entries.sum().float(), q_entries.sum().float()
+    p = p_entries * binsizes / n_p
+    q = ((q_entries + 1e-6) * binsizes / n_q).log()
+    return F.kl_div(q, p, reduction="sum") / binsizes.mean()
+
+
 def generator_loss(gen: Sequence[Tensor], hr: Tensor, lr: Tensor, d_sds: Sequence[SD], *, factor: int,
                    scaling_power: float = 1.0, lambdas=(0.2, 1.0), lambda_hr=1.0, lambda_lr=0.1,
-                   lambda_adv=0.01) -> Tuple[Tensor, Dict[str, Tensor]]:
-    """G-step loss assembly, esrgan.py:468-552 with the default.json weights.
-    ``gen`` = (generator output, generator.srs)."""
+                   lambda_adv=0.01, lambda_nnz=0.0, lambda_mask=0.0, lambda_hist=0.0, lambda_hit=0.0,
+                   binedges: Optional[Sequence[Tensor]] = None, sigma: float = 500, hit_threshold: float = 0.5
+                   ) -> Tuple[Tensor, Dict[str, Tensor]]:
+    """G-step loss assembly, esrgan.py:468-552 with the default.json weights (+ the optional nnz / mask / hist / hit
+    terms of 530-550 when their lambda is > 0).  ``gen`` = (generator output, generator.srs)."""
     ground_truth = (hr, hr ** scaling_power)                                  # 470
     gen_lr = sum_pool(gen[0], factor)                                         # 471
     generated_lr = (gen_lr, gen_lr ** scaling_power)                          # 472
@@ -310,6 +347,23 @@ def generator_loss(gen: Sequence[Tensor], hr: Tensor, lr: Tensor, d_sds: Sequenc
         pred_fake = discriminator_forward(d_sds[k], gen[k])                     # 494
         l_adv = ragan_loss_g(pred_real, pred_fake)                              # 507
         tot = lambda_hr * l_hr + lambda_adv * l_adv + lambda_lr * l_lr          # 549
+        if lambda_nnz > 0:                                                      # 530-533
+            gen_nnz = softgreater(gen[k], 0, 50000).sum(1).sum(1).sum(1)
+            target = (ground_truth[k] > 0).sum(1).sum(1).sum(1).float()
+            parts[f"nnz{k}"] = F.mse_loss(gen_nnz, target)
+            tot = tot + lambda_nnz * parts[f"nnz{k}"]
+        if lambda_mask > 0:                                                     # 534-537
+            parts[f"mask{k}"] = F.l1_loss(nnz_mask(gen[k]), nnz_mask(ground_truth[k]))
+            tot = tot + lambda_mask * parts[f"mask{k}"]
+        if lambda_hist > 0:                                                     # 538-545
+            gen_hist = diffable_histogram(gen[k][gen[k] > 0], binedges[k], sigma)
+            real_hist = diffable_histogram(ground_truth[k][ground_truth[k] > 0], binedges[k], sigma)
+            parts[f"hist{k}"] = kld_hist(gen_hist, real_hist, binedges[k])
+            tot = tot + lambda_hist * parts[f"hist{k}"]
+        if lambda_hit > 0:                                                      # 546-550
+            parts[f"hit{k}"] = F.mse_loss(get_hitogram(gen[k], factor, hit_threshold, sigma),
+                                          get_hitogram(ground_truth[k], factor, hit_threshold, sigma))
+            tot = tot + lambda_hit * parts[f"hit{k}"]
         loss_g = loss_g + lambdas[k] * tot                                      # 552
         parts[f"hr{k}"], parts[f"lr{k}"], parts[f"adv{k}"] = l_hr, l_lr, l_adv
     return loss_g, parts

@@ -22,6 +22,7 @@
 #include "disc.cu"
 #include "disc_mma.cu"
 #include "optim_loss.cu"
+#include "opt_losses.cu"
 #include "data_path.cu"
 #include "eval_stats.cu"
 #include "api.cu"

@@ -117,3 +117,68 @@ class GradientPenalty(torch.autograd.Function):
         L.check(L.lib().srb_gp_bwd(gc.data_ptr(), norms.data_ptr(), B, n, float(ctx.coef), glc.data_ptr(),
                                    gg.data_ptr(), _st()), "gp_bwd")
         return gg, None
+
+
+# ---------------------------------------------------------------------------------------------- optional terms
+class OptionalLossWork:
+    """Scratch + constants of the optional generator loss terms (csrc/opt_losses.cu) for one (B, H, W)."""
+
+    def __init__(self, B, H, W, factor, dev, binedges=None):
+        self.B, self.H, self.W, self.f = B, H, W, factor
+        self.per_image = torch.empty(B, device=dev)
+        self.hit = torch.zeros(2 * factor * factor, device=dev)
+        self.bins = None
+        if binedges is not None:       # per branch k: (centers, deltas) of DiffableHistogram built from the bin edges
+            self.bins = []
+            for e in binedges:
+                e = torch.as_tensor(e, dtype=torch.float32, device=dev)
+                d = (e[1:] - e[:-1]).contiguous()
+                self.bins.append(dict(centers=(e[:-1] + 0.5 * d).contiguous(), deltas=d, n=int(d.numel()),
+                                      hq=torch.zeros(d.numel(), device=dev), hp=torch.zeros(d.numel(), device=dev),
+                                      dq=torch.zeros(d.numel(), device=dev)))
+
+
+def nnz_loss(gen, gt, w, grad, work: OptionalLossWork, sigma=50000.0):
+    """esrgan.py:530-533; adds w * d loss / d gen into ``grad``."""
+    g, t = _c(gen), _c(gt)
+    B = g.shape[0]
+    loss = torch.empty((), device=g.device)
+    L.check(L.lib().srb_nnz_loss(g.data_ptr(), t.data_ptr(), B, g[0].numel(), float(sigma), float(w), 1,
+                                 work.per_image.data_ptr(), loss.data_ptr(), grad.data_ptr(), _st()), "nnz_loss")
+    return loss
+
+
+def mask_loss(gen, gt, w, grad, sigma=5e4):
+    """esrgan.py:534-537."""
+    g, t = _c(gen), _c(gt)
+    loss = torch.empty((), device=g.device)
+    L.check(L.lib().srb_mask_loss(g.data_ptr(), t.data_ptr(), g.numel(), float(sigma), float(w), 1, loss.data_ptr(),
+                                  grad.data_ptr(), _st()), "mask_loss")
+    return loss
+
+
+def hit_loss(gen, gt, factor, thr, sig, w, grad, work: OptionalLossWork):
+    """esrgan.py:546-550."""
+    g, t = _c(gen), _c(gt)
+    B, _, H, W = g.shape
+    loss = torch.empty((), device=g.device)
+    L.check(L.lib().srb_hit_loss(g.data_ptr(), t.data_ptr(), B, H, W, int(factor), float(thr), float(sig), float(w), 1,
+                                 work.hit.data_ptr(), loss.data_ptr(), grad.data_ptr(), _st()), "hit_loss")
+    return loss
+
+
+def hist_loss(gen, gt, k, sigma, w, grad, work: OptionalLossWork):
+    """esrgan.py:538-545: KLD_hist(DiffableHistogram(gen[gen > 0]), DiffableHistogram(gt[gt > 0]))."""
+    g, t = _c(gen), _c(gt)
+    b = work.bins[k]
+    lib = L.lib()
+    L.check(lib.srb_soft_hist(g.data_ptr(), g.numel(), b["centers"].data_ptr(), b["deltas"].data_ptr(), b["n"],
+                              float(sigma), b["hq"].data_ptr(), _st()), "soft_hist")
+    L.check(lib.srb_soft_hist(t.data_ptr(), t.numel(), b["centers"].data_ptr(), b["deltas"].data_ptr(), b["n"],
+                              float(sigma), b["hp"].data_ptr(), _st()), "soft_hist")
+    loss = torch.empty((), device=g.device)
+    L.check(lib.srb_kld_hist(b["hq"].data_ptr(), b["hp"].data_ptr(), b["deltas"].data_ptr(), b["n"], loss.data_ptr(),
+                             b["dq"].data_ptr(), _st()), "kld_hist")
+    L.check(lib.srb_soft_hist_bwd(g.data_ptr(), g.numel(), b["centers"].data_ptr(), b["deltas"].data_ptr(), b["n"],
+                                  float(sigma), b["dq"].data_ptr(), float(w), 1, grad.data_ptr(), _st()), "soft_hist_bwd")
+    return loss

@@ -36,13 +36,22 @@ class GANTrainStep:
                  lambda_lr=0.1, lambda_adv=0.01, lambda_reg=0.01, d_threshold=0.001, lr=2e-4, lr_g=0.0, lr_d=0.0,
                  betas=(0.9, 0.999), l2decay=0.0, scaling_power=1.0, process_group=None, use_disc_engine=True,
                  second_discriminators: Optional[Sequence] = None, second_discr_reset_interval: int = 0,
-                 uniform_reset: bool = False):
+                 uniform_reset: bool = False, lambda_nnz=0.0, lambda_mask=0.0, lambda_hist=0.0, lambda_hit=0.0,
+                 binedges=None, sigma=500.0, hit_threshold=0.5):
         """``scaling_power``: opt.scaling_power (esrgan.py:470-473): the "pow" branch (k = 1) compares generator.srs with
         hr ** p, the pooled image ** p with lr ** p, and shows D_pow the powered images; the generator must have been
         built with power=p.  ``second_discriminators``: the SecondDiscriminators ensemble of esrgan.py:221-237 (one per
         branch): the adversarial term averages both discriminators (495-505), both are trained every iteration
         (565-620, stepping together on the first one's d_threshold test, 623-626) and the second ones are
-        re-initialised every ``second_discr_reset_interval`` iterations (789-795)."""
+        re-initialised every ``second_discr_reset_interval`` iterations (789-795).
+        ``lambda_nnz / lambda_mask / lambda_hist / lambda_hit``: the optional terms of esrgan.py:530-550 on fused kernels
+        (csrc/opt_losses.cu); ``binedges`` = per branch the histogram bin edges esrgan.py:440-450 derives during warm-up
+        (info['binedges0'], info['binedges1']), ``sigma`` = opt.sigma, ``hit_threshold`` = opt.hit_threshold.  The
+        sorted-Wasserstein / Sinkhorn term (lambda_wasser, esrgan.py:539-542) is not part of the fused step."""
+        self.l_nnz, self.l_mask, self.l_hist, self.l_hit = lambda_nnz, lambda_mask, lambda_hist, lambda_hit
+        self.binedges, self.sigma, self.hit_threshold = binedges, float(sigma), float(hit_threshold)
+        if lambda_hist > 0 and binedges is None:
+            raise RuntimeError("CUDA srb200: lambda_hist > 0 needs the bin edges (esrgan.py:440-450)")
         self.power = float(scaling_power)
         self.G, self.Ds = generator, list(discriminators)
         self.D2s = list(second_discriminators) if second_discriminators is not None else [None] * len(self.Ds)
@@ -118,7 +127,8 @@ class GANTrainStep:
         w = self._work.get(key)
         if w is None:
             w = dict(w0=LS.PixelLossWork(B, H, W, self.factor, dev), w1=LS.PixelLossWork(B, H, W, self.factor, dev),
-                     g0=torch.empty(B, 1, H, W, device=dev), g1=torch.empty(B, 1, H, W, device=dev))
+                     g0=torch.empty(B, 1, H, W, device=dev), g1=torch.empty(B, 1, H, W, device=dev),
+                     opt=LS.OptionalLossWork(B, H, W, self.factor, dev, self.binedges))
             self._work[key] = w
         return w
 
@@ -163,6 +173,21 @@ class GANTrainStep:
                                    wk["w1"])
         out_losses.update(hr0=l_hr0, lr0=l_lr0, hr1=l_hr1, lr1=l_lr1)
         loss_G = lam0 * (self.l_hr * l_hr0 + self.l_lr * l_lr0) + lam1 * (self.l_hr * l_hr1 + self.l_lr * l_lr1)
+        # optional terms (esrgan.py:530-550), each fused with its gradient w.r.t. generated[k]
+        for k in range(2):
+            lam = self.lambdas[k]
+            if lam <= 0:
+                continue
+            for name, coef, fn in (
+                    ("nnz", self.l_nnz, lambda c: LS.nnz_loss(generated[k], truth[k], c, g[k], wk["opt"])),
+                    ("mask", self.l_mask, lambda c: LS.mask_loss(generated[k], truth[k], c, g[k])),
+                    ("hist", self.l_hist, lambda c: LS.hist_loss(generated[k], truth[k], k, self.sigma, c, g[k], wk["opt"])),
+                    ("hit", self.l_hit, lambda c: LS.hit_loss(generated[k], truth[k], self.factor, self.hit_threshold,
+                                                              self.sigma, c, g[k], wk["opt"]))):
+                if coef > 0:
+                    l_ = fn(lam * coef)
+                    out_losses[f"{name}{k}"] = l_
+                    loss_G = loss_G + lam * coef * l_
         main0 = torch.cuda.current_stream()
         active = [k for k in range(2) if not (self.lambdas[k] <= 0 or self.Ds[k] is None or self.l_adv <= 0)]
         use_streams = self.d_streams and len(active) == 2 and \

@@ -17,6 +17,8 @@ import ref_harness  # noqa: E402
 VARIANTS = {      # small runs of the non-default training recipes the fused step also covers
     "scaling_power_0.5": dict(scaling_power=0.5),                   # esrgan.py:470-473: the "pow" branch on x ** 0.5
     "second_discriminators": dict(second_discr_reset_interval=4),   # esrgan.py:221-237,495-505,789-795
+    "optional_losses": dict(lambda_nnz=1e-4, lambda_mask=0.5, lambda_hit=2.0),          # esrgan.py:530-537,546-550
+    "hist": dict(lambda_hist=0.1, warmup_batches=2, bins=6),        # esrgan.py:433-452,538-545 (2 warm-up steps first)
 }
 
 if __name__ == "__main__":

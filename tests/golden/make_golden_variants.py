@@ -20,8 +20,8 @@ CASES = {
     "tconv_alternating": dict(nb=1, nup=2, lr=10, batch=3, kw=dict(use_transposed_conv=True)),
     "tconv_full": dict(nb=1, nup=2, lr=10, batch=3, kw=dict(fully_tconv_upsample=True)),
     "final_res_1": dict(nb=1, nup=1, lr=12, batch=3, kw=dict(num_final_layer_res=1)),
-    "final_res_2_tconv": dict(nb=2, nup=2, lr=6, batch=2, kw=dict(num_final_layer_res=2, use_transposed_conv=True)),
-    "dropout": dict(nb=2, nup=1, lr=12, batch=4, kw=dict(drop_rate=0.3)),
+    "final_res_2_tconv": dict(nb=2, nup=2, lr=10, batch=6, kw=dict(num_final_layer_res=2, use_transposed_conv=True)),
+    "dropout": dict(nb=2, nup=1, lr=16, batch=10, kw=dict(drop_rate=0.3)),
     "dropout_final": dict(nb=1, nup=1, lr=10, batch=3, kw=dict(drop_rate=0.25, num_final_layer_res=1)),
 }
 

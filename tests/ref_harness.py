@@ -165,10 +165,11 @@ def run(ref_root, models_dir=None, *, n_batches=20, batch_size=16, seed=4321, fa
         with open(os.path.join(tmp, "saved_models", "_info.json")) as f:      # model_name = opt.name + '_' (esrgan.py:153)
             info = json.load(f)
         loss = {k: [float(x) for x in v] for k, v in (info.get("loss") or {}).items()}
+        extra = {k: v for k, v in info.items() if k.startswith("binedges")}
         if not loss:
             raise RuntimeError("reference train() returned no loss trace")
         return {"loss": loss, "order": rec["order"], "epsilons": rec["epsilons"], "init_checksums": sums,
-                "step_t": rec["t"][0::2],
+                "step_t": rec["t"][0::2], "info_extra": extra,
                 "cfg": dict(n_batches=n_batches, batch_size=batch_size, seed=seed, factor=factor,
                             residual_blocks=residual_blocks, overrides=overrides or {}),
                 "models_file": models_file, "device": "cuda" if torch.cuda.is_available() else "cpu",
