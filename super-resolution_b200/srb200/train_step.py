@@ -80,6 +80,7 @@ class GANTrainStep:
         # steps, the generator's backward pass); inside the CUDA graph these are parallel branches.
         self.d_streams = os.environ.get("SRB_D_STREAMS", "1") == "1"
         self._k_streams = None
+        self.marks = None            # tools/phase_breakdown.py: list that receives (phase name, CUDA event) on the main stream
         # bucketed gradient all-reduce overlapped with the generator's backward (srb200/dp.py)
         self._g_sync = DP.BucketedAllReduce(self.opt_G.flat_g, process_group) if self.world > 1 else None
         self._g_off = {n: o for (n, _), o in zip(((n, p) for n, p in generator.named_parameters() if p.requires_grad),
@@ -91,6 +92,12 @@ class GANTrainStep:
             return DE.DiscEngine(d.model, d.input_shape) if ok else None
         self.d_eng = [engine_for(d) for d in self.Ds]
         self.d2_eng = [engine_for(d) for d in self.D2s]
+
+    def _mark(self, name: str) -> None:
+        if self.marks is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self.marks.append((name, e))
 
     def _members(self, k):
         """(discriminator, engine, optimizer, key suffix) of branch k: the discriminator and, if configured, its
@@ -150,9 +157,11 @@ class GANTrainStep:
         out_losses: Dict[str, torch.Tensor] = {}
 
         # ---------------- generator ----------------
+        self._mark("start")
         out, srs = eng.forward(imgs_lr, power=G._host_scalar("power"), multiplier=G._host_scalar("multiplier"),
                                thres=float(G.thres), training=G.training, save_for_backward=True)
         G.srs = srs
+        self._mark("generator forward")
         generated = (out, srs)
         g = (wk["g0"], wk["g1"])
         p = self.power
@@ -230,6 +239,7 @@ class GANTrainStep:
             out_losses[f"adv{k}"] = l_adv.detach()
         for ev in adv_done:
             main0.wait_event(ev)                # the generator's backward pass needs both adversarial gradients
+        self._mark("losses + discriminator forward / input gradient")
         for k in active:
             loss_G = loss_G + self.lambdas[k] * self.l_adv * out_losses[f"adv{k}"]
         main = torch.cuda.current_stream()
@@ -243,13 +253,16 @@ class GANTrainStep:
             eng.ready_hook = lambda name: self._g_sync.mark_ready(self._g_off[name])
         grads = eng.backward(g[0], g[1])                                                   # esrgan.py:553
         eng.ready_hook = None
+        self._mark("generator backward (buckets all-reduced beside it)")
         for n, p in G.named_parameters():
             if p.requires_grad:
                 p.grad = grads[n]                      # views of the optimizer's flat gradient buffer: no copy
         self.opt_G.gather_grads()
         if self._g_sync is not None:
             self._g_sync.finish()
+        self._mark("wait for the last gradient bucket")
         self.opt_G.step(grad_scale=1.0 / self.world, gathered=True)                        # esrgan.py:555
+        self._mark("generator Adam")
         out_losses["g_loss"] = loss_G
         if use_streams:
             # each discriminator's training step continues on ITS stream (ordered after its own forward / input
@@ -275,6 +288,7 @@ class GANTrainStep:
             main.wait_event(join)
         else:
             self._discriminator_steps(truth, generated, epsilons, out_losses, B, dev)
+        self._mark("discriminator steps (joined)")
         if not torch.cuda.is_current_stream_capturing():
             self.end_of_batch()
         return out_losses
