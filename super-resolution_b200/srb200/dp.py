@@ -35,7 +35,13 @@ def make_buckets(n: int, bucket_elems: int) -> List[Tuple[int, int]]:
 
 
 class BucketedAllReduce:
-    def __init__(self, flat: torch.Tensor, group=None, bucket_bytes: int = 24 << 20):
+    def __init__(self, flat: torch.Tensor, group=None, bucket_bytes: Optional[int] = None):
+        # 8 MB buckets: the LAST bucket (conv1 + the first RRDBs) can only start when backward is over, so its size is
+        # what the step waits for (measured at N = 2 with 24 MB buckets: 0.37 ms exposed, profiles/r02_s7_phase_*);
+        # SRB_DP_BUCKET_MB overrides
+        if bucket_bytes is None:
+            import os
+            bucket_bytes = int(float(os.environ.get("SRB_DP_BUCKET_MB", "8")) * (1 << 20))
         self.flat, self.group = flat, group
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
         self.buckets = make_buckets(flat.numel(), bucket_bytes // flat.element_size())
