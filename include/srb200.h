@@ -162,6 +162,17 @@ size_t srb_wgrad3x3_workspace_bytes(int batch, int H, int W, int cin, int cout);
  * buffer.  items[0].workspace must hold srb_wgrad3x3_group_workspace_bytes(...). */
 int srb_wgrad3x3_group(const srb_wgrad3x3_args* items, int n, void* stream);
 size_t srb_wgrad3x3_group_workspace_bytes(int batch, int H, int W, int n, const int* cin, const int* cout);
+/* Allocation-free variant of srb_wgrad3x3.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments and results as srb_wgrad3x3 on the tcgen05 kernel; a->workspace / workspace_bytes / impl
+ * are ignored: the split-K scratch is a static device array inside the library, srb_wgrad3x3_static_max_bytes() =
+ * 16 MiB, held by every GPU that loads the library until the process exits.  A problem whose
+ * srb_wgrad3x3_workspace_bytes(...) exceeds that is rejected (returns 1, srb_last_error() names both sizes).  The call
+ * allocates nothing (no cudaMalloc / cudaFree / allocating library routine); its first use on a device looks the
+ * array's address up once (cudaGetSymbolAddress).  All calls share the array: calls that overlap on the GPU (two streams,
+ * two host threads) race on it - serialise them on one stream. */
+int srb_wgrad3x3_static(const srb_wgrad3x3_args* a, void* stream);
+size_t srb_wgrad3x3_static_max_bytes(void);
 
 /* ---- bandwidth-bound ends of the generator (csrc/gen_edge.cu) ------------------------------------
  * srb_conv_in_fwd : models.py:122-123  multiplier*x**power -> conv1; fp32 NCHW image -> PNHWC bf16 (two optional dsts)

@@ -22,6 +22,9 @@
 // Work item = (unit, 64-wide output-channel block, K split).  Each CTA accumulates its whole K range in 192 TMEM
 // columns per issuer, then writes partial [3 taps][64 ci][64 co] fp32 tiles (one per half) to the workspace; a second
 // kernel reduces the K splits, scales, and scatters to OIHW (state_dict layout).
+#include <mutex>
+#include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -398,4 +401,61 @@ extern "C" int srb_wgrad3x3_group(const srb_wgrad3x3_args* items, int n, void* s
   for (int i = 0; i < n; ++i)
     if (!items[i].x || !items[i].gy || !items[i].dw) return srb::set_error("wgrad3x3 group: null pointer");
   return srb::wgrad3x3_tc_launch_group(items, n, (cudaStream_t)stream);
+}
+
+// ---- allocation-free variant: split-K scratch in a static device array ------------------------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).  No counterpart
+// in the reference.  The array is part of the library image: every GPU
+// that loads libsrb200 holds kWgStaticWsBytes of it until the process exits.  All calls share it and it keeps the last
+// call's contents: the partial tiles need no clearing (every tile the reduction reads is overwritten by the main kernel
+// of the same call), the bias column sums at its tail are cleared by the call itself.  Two calls that overlap on the
+// GPU (different streams, or two host threads) race on it.
+constexpr size_t kWgStaticWsBytes = size_t(16) << 20;      // 16 MiB: any single 3x3 problem up to cin * cout = 320 * 64
+static __device__ __align__(256) unsigned char g_wgrad_static_ws[kWgStaticWsBytes];
+
+namespace srb {
+// In host code g_wgrad_static_ws is only a handle of the symbol, not a device address: the address is looked up once per
+// device, with that device current, and that pointer is what the kernels get.
+static int wgrad_static_ws_ptr(void** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static void* ptr[kMaxDev] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return set_cuda_error("wgrad3x3_static: cudaGetDevice", e);
+  if (dev < 0 || dev >= kMaxDev) return set_error("wgrad3x3_static: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_wgrad_static_ws);
+    if (e != cudaSuccess || !p) return set_cuda_error("wgrad3x3_static: cudaGetSymbolAddress", e);
+    if (reinterpret_cast<uintptr_t>(p) & 255) return set_error("wgrad3x3_static: scratch array is not 256-byte aligned");
+    ptr[dev] = p;
+  }
+  *out = ptr[dev];
+  return 0;
+}
+}  // namespace srb
+
+extern "C" size_t srb_wgrad3x3_static_max_bytes(void) { return kWgStaticWsBytes; }
+
+extern "C" int srb_wgrad3x3_static(const srb_wgrad3x3_args* a, void* stream) {
+  if (!a || !a->x || !a->gy || !a->dw) return srb::set_error("wgrad3x3_static: null pointer");
+  if (a->cin <= 0 || a->cout <= 0 || a->cin % 64 || a->cout % 64)
+    return srb::set_error("wgrad3x3_static: channels must be multiples of 64");
+  if (a->batch <= 0 || a->H <= 0 || a->W <= 0) return srb::set_error("wgrad3x3_static: bad geometry");
+  const size_t need = srb_wgrad3x3_workspace_bytes(a->batch, a->H, a->W, a->cin, a->cout);
+  if (need > kWgStaticWsBytes) {
+    char msg[256];
+    snprintf(msg, sizeof(msg), "wgrad3x3_static: this problem needs %zu bytes of split-K scratch, the built-in array "
+             "holds %zu (use srb_wgrad3x3 with a caller-owned workspace)", need, (size_t)kWgStaticWsBytes);
+    return srb::set_error(msg);
+  }
+  void* ws = nullptr;
+  if (srb::wgrad_static_ws_ptr(&ws)) return 1;
+  srb_wgrad3x3_args b = *a;
+  b.workspace = ws;
+  b.workspace_bytes = kWgStaticWsBytes;
+  b.impl = SRB_IMPL_TCGEN05;
+  return srb::wgrad3x3_tc_launch(&b, (cudaStream_t)stream);
 }

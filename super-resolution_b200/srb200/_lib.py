@@ -111,6 +111,8 @@ _SIGS = {
     "srb_pack_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "srb_wgrad3x3": (C.c_int, [C.POINTER(Wgrad3x3Args), C.c_void_p]),
     "srb_wgrad3x3_group": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "srb_wgrad3x3_static": (C.c_int, [C.POINTER(Wgrad3x3Args), C.c_void_p]),
+    "srb_wgrad3x3_static_max_bytes": (C.c_size_t, []),
     "srb_wgrad3x3_group_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "srb_wgrad3x3_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "srb_conv_in_fwd": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p,
