@@ -36,8 +36,11 @@ def data(r):
 
 G, Ds, tr = build(dist.group.WORLD)
 hr, lr, eps = data(rank)
-for _ in range(2):
+g_first = {}
+for it in range(2):
     losses = tr.step(lr, hr, epsilons=eps)
+    if it == 0:     # flat_g after a DP step = the all-reduced SUM of the ranks' gradients (Adam applies 1 / world)
+        g_first = {k: o.flat_g.clone() for k, o in (("G", tr.opt_G), ("D0", tr.opt_D[0]), ("D1", tr.opt_D[1]))}
 torch.cuda.synchronize()
 # all ranks hold identical parameters
 for name, flat in (("G", tr.opt_G.flat_p), ("D0", tr.opt_D[0].flat_p), ("D1", tr.opt_D[1].flat_p)):
@@ -60,6 +63,14 @@ if rank == 0:
             t.step(l, h, epsilons=e)
             saved.append(snap)
         from srb200.optim import FusedAdam
+        if it == 0:
+            # step 0 starts from identical parameters: NCCL's sum and the hand sum differ only by fp32 summation order
+            # (at 2 ranks not at all; rings / trees / NVLS at 8 ranks add in another order)
+            for key in ("G", "D0", "D1"):
+                hand = sum(s[key][0] for s in saved)
+                d, m = (g_first[key] - hand).abs().max().item(), hand.abs().max().item()
+                print(f"{key}: step-0 gradient  max |allreduce - hand sum| = {d:.3e}  (|g| max {m:.3e})", flush=True)
+                assert d <= 1e-5 * m, key
         for (Gr, Dr, t) in reps:
             for key, opt in (("G", t.opt_G), ("D0", t.opt_D[0]), ("D1", t.opt_D[1])):
                 opt.step = FusedAdam.step.__get__(opt)
@@ -69,11 +80,16 @@ if rank == 0:
                     gate = (sum(s[key][1] for s in saved) / world, t.d_threshold)
                 opt.step(gate=gate, grad_scale=1.0 / world, gathered=True)
     torch.cuda.synchronize()
+    # Adam's first steps move every element by ~lr * g / (|g| + eps): where |g| is at the fp32 noise of the sum, another
+    # summation order can flip that element's whole step (2e-4).  So: all but 1e-4 of the elements within 2e-5, and no
+    # element further than the two steps' bound 2 * 2 * lr.
     for key, a, b in (("G", tr.opt_G.flat_p, reps[0][2].opt_G.flat_p), ("D0", tr.opt_D[0].flat_p, reps[0][2].opt_D[0].flat_p),
                       ("D1", tr.opt_D[1].flat_p, reps[0][2].opt_D[1].flat_p)):
-        d = (a - b).abs().max().item()
-        print(f"{key}: max |dp - replay| = {d:.3e}  (|p| max {a.abs().max().item():.3e})")
-        assert d <= 2e-5, key
-    print("dp_check ok", {k: float(v) for k, v in losses.items()})
+        diff = (a - b).abs()
+        d, frac = diff.max().item(), (diff > 2e-5).float().mean().item()
+        print(f"{key}: max |dp - replay| = {d:.3e}, fraction beyond 2e-5 = {frac:.2e}  (|p| max {a.abs().max().item():.3e})",
+              flush=True)
+        assert d <= 8.1e-4 and frac <= 1e-4, key
+    print("dp_check ok", {k: float(v) for k, v in losses.items()}, flush=True)
 dist.barrier()
 dist.destroy_process_group()
