@@ -215,6 +215,9 @@ def time_cpu(batch, steps, warmup, cfg):
     return batch / dt, dt
 
 
+CPU_SAMPLE_STEPS = 20      # in-run cpu_baseline sample: ~10 s of host work at 0.5 s per batch-16 step
+
+
 def time_reference_train(batch, steps, warmup, cfg):
     """The UNMODIFIED reference (baseline/_ref, a copy of the reference tree made by __graft_entry__.build()) through
     its own esrgan.train() on the host cores: tests/ref_harness.py supplies opt, an in-memory synthetic dataset and
@@ -244,7 +247,7 @@ def run_reference(args):
     if rank != 0:
         return
     cfg = CONFIGS["deep" if args.config == "deep" else "gan"]
-    steps, warm = max(1, min(args.steps, 5)), max(1, min(args.warmup, 1))
+    steps, warm = max(1, min(args.steps, 20)), max(1, min(args.warmup, 2))
     kind, how = "port", (f"batch {args.cpu_batch} per step on the host cores (oracle/oracle.py, torch CPU fp32; pinned "
                          "against the reference's own esrgan.train trace, tests/test_trace_oracle.py)")
     if os.path.isdir(os.path.join(ROOT, "baseline", "_ref")):
@@ -536,13 +539,13 @@ def run_ours(args):
         try:
             if not os.path.isdir(os.path.join(ROOT, "baseline", "_ref")):
                 raise FileNotFoundError("baseline/_ref")
-            ips, dt = time_reference_train(args.cpu_batch, 3, 1, cfg)
+            ips, dt = time_reference_train(args.cpu_batch, CPU_SAMPLE_STEPS, 1, cfg)
             kind, what = "reference", "the unmodified reference's own esrgan.train() (baseline/_ref) via tests/ref_harness.py"
         except Exception:  # noqa: BLE001
-            ips, dt = time_cpu(args.cpu_batch, 3, 1, cfg)
+            ips, dt = time_cpu(args.cpu_batch, CPU_SAMPLE_STEPS, 1, cfg)
             what = "oracle/oracle.py (torch CPU fp32, the reference's own backend)"
         cpu_baseline = {"value": ips, "unit": "images/s", "cores": os.cpu_count() or 1, "kind": kind,
-                        "sample": f"3 GAN steps of batch {args.cpu_batch} ({dt:.2f} s/step) on the host cores, " + what}
+                        "sample": f"{CPU_SAMPLE_STEPS} GAN steps of batch {args.cpu_batch} ({dt:.2f} s/step, median) on the host cores, " + what}
     gpu_baseline = None
     if rank == 0 and world == 1 and not args.no_extras and not args.no_gpu_baseline and args.config == "gan":
         # the bar SURVEY.md section 2a sets: the reference's modules under stock PyTorch / cuDNN on this GPU
