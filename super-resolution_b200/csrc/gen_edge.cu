@@ -52,53 +52,86 @@ __global__ void conv_in_fwd_kernel(const float* __restrict__ img, int B, int Cim
 }
 
 // ---------------------------------------------------------------- conv_in backward (weights only)
-// dW[f][c][t] += sum_p g[p][f] * xin[p + s_t][c];  db[f] += sum_p g[p][f].   grid.x = pixel chunks;
-// block = 256 threads = F(64) x 4 pixel lanes (F <= 64 per blockIdx.y slice).
-__global__ void conv_in_bwd_kernel(const float* __restrict__ img, int B, int Cimg, int H, int W, float multiplier,
-                                   float power, const __nv_bfloat16* __restrict__ g, int g_cstride, int g_coff,
-                                   const __nv_bfloat16* __restrict__ g2, int g2_cstride, int g2_coff, int F,
-                                   float* __restrict__ dw, float* __restrict__ db, int pix_per_block) {
-  const int f = blockIdx.y * 64 + (threadIdx.x & 63);
-  const int pl = threadIdx.x >> 6;
+// dW[f][c][t] += sum_p g[p][f] * xin[p + s_t][c];  db[f] += sum_p g[p][f].
+// One warp walks a contiguous range of pixels with a running (b, y, x) counter (no per-pixel divisions); a lane owns
+// one channel pair of the 64-wide slice blockIdx.y, so a pixel's gradient row is one coalesced 128-byte load, four
+// pixels' loads in flight per warp.  The image taps are warp-uniform: zero taps (jet images are >99 % zeros) skip their
+// FMAs.  Warps of a block meet in shared memory, blocks in global atomics.
+template <int CC>                                      // image channels (1..4): sizes the accumulator registers
+__global__ void __launch_bounds__(256)
+conv_in_bwd_kernel(const float* __restrict__ img, int B, int Cimg, int H, int W, float multiplier,
+                   float power, const __nv_bfloat16* __restrict__ g, int g_cstride, int g_coff,
+                   const __nv_bfloat16* __restrict__ g2, int g2_cstride, int g2_coff, int F,
+                   float* __restrict__ dw, float* __restrict__ db, int pix_per_warp) {
+  __shared__ float red[37 * 64];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int fl = lane * 2, f = blockIdx.y * 64 + fl;
+  const bool fok = f < F;
+  for (int i = threadIdx.x; i < 37 * 64; i += 256) red[i] = 0.f;
+  __syncthreads();
   const long long npix = 1LL * B * H * W;
-  const long long p0 = 1LL * blockIdx.x * pix_per_block;
-  long long p1 = p0 + pix_per_block; if (p1 > npix) p1 = npix;
-  float acc[9 * 4];   // up to 4 image channels
+  const long long p0 = (1LL * blockIdx.x * 8 + warp) * pix_per_warp;
+  long long p1 = p0 + pix_per_warp; if (p1 > npix) p1 = npix;
+  float acc[CC][9][2];
 #pragma unroll
-  for (int i = 0; i < 36; ++i) acc[i] = 0.f;
-  float bsum = 0.f;
-  const int Cc = Cimg < 4 ? Cimg : 4;
-  for (long long pidx = p0 + pl; pidx < p1; pidx += 4) {
-    const int px = int(pidx % W); const int py = int((pidx / W) % H); const int b = int(pidx / (1LL * W * H));
-    const size_t row = (static_cast<size_t>(b) * (H + 1) + py) * (W + 1) + px;
-    float gv = f < F ? __bfloat162float(g[row * g_cstride + g_coff + f]) : 0.f;
-    if (g2 && f < F) gv += __bfloat162float(g2[row * g2_cstride + g2_coff + f]);
-    bsum += gv;
-    if (gv == 0.f) continue;
-    for (int c = 0; c < Cc; ++c) {
-      const float* ip = img + (static_cast<size_t>(b) * Cimg + c) * H * W;
+  for (int c = 0; c < CC; ++c)
 #pragma unroll
-      for (int t = 0; t < 9; ++t) {
-        const int yy = py + t / 3 - 1, xx = px + t % 3 - 1;
-        if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;
-        float v = ip[yy * W + xx];
-        if (power != 1.f) v = powf(v, power);
-        acc[c * 9 + t] += gv * v * multiplier;
+    for (int t = 0; t < 9; ++t) acc[c][t][0] = acc[c][t][1] = 0.f;
+  float bs0 = 0.f, bs1 = 0.f;
+  if (p0 < p1) {
+    int px = int(p0 % W), py = int((p0 / W) % H), b = int(p0 / (1LL * W * H));
+    const int n = int(p1 - p0);
+    for (int i0 = 0; i0 < n; i0 += 4) {
+      uint32_t gw[4], gw2[4];
+      int bb[4], yy[4], xx[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        bb[j] = b; yy[j] = py; xx[j] = px;
+        const size_t row = (static_cast<size_t>(b) * (H + 1) + py) * (W + 1) + px;
+        const bool ok = fok && i0 + j < n;
+        gw[j] = ok ? __ldg(reinterpret_cast<const uint32_t*>(g + row * g_cstride + g_coff + f)) : 0u;
+        gw2[j] = (ok && g2) ? __ldg(reinterpret_cast<const uint32_t*>(g2 + row * g2_cstride + g2_coff + f)) : 0u;
+        if (++px == W) { px = 0; if (++py == H) { py = 0; ++b; } }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (i0 + j >= n) break;
+        const float g0 = bf16lo(gw[j]) + bf16lo(gw2[j]), g1 = bf16hi(gw[j]) + bf16hi(gw2[j]);
+        bs0 += g0; bs1 += g1;
+#pragma unroll
+        for (int c = 0; c < CC; ++c) {
+          const float* ip = img + (static_cast<size_t>(bb[j]) * Cimg + c) * H * W;
+#pragma unroll
+          for (int t = 0; t < 9; ++t) {
+            const int y2 = yy[j] + t / 3 - 1, x2 = xx[j] + t % 3 - 1;
+            if (y2 < 0 || y2 >= H || x2 < 0 || x2 >= W) continue;
+            float v = __ldg(ip + y2 * W + x2);
+            if (v == 0.f && power > 0.f) continue;                 // warp-uniform: every lane reads the same tap
+            if (power != 1.f) v = powf(v, power);
+            v *= multiplier;
+            acc[c][t][0] += g0 * v; acc[c][t][1] += g1 * v;
+          }
+        }
       }
     }
   }
-  __shared__ float red[4][64][37];
 #pragma unroll
-  for (int i = 0; i < 36; ++i) red[pl][threadIdx.x & 63][i] = acc[i];
-  red[pl][threadIdx.x & 63][36] = bsum;
-  __syncthreads();
-  if (pl == 0 && f < F) {
-    for (int i = 0; i < Cc * 9; ++i) {
-      const float s = red[0][threadIdx.x][i] + red[1][threadIdx.x][i] + red[2][threadIdx.x][i] + red[3][threadIdx.x][i];
-      if (s != 0.f) atomicAdd(dw + (static_cast<size_t>(f) * Cimg + i / 9) * 9 + i % 9, s);
+  for (int c = 0; c < CC; ++c) {
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      if (acc[c][t][0] != 0.f) atomicAdd(&red[(c * 9 + t) * 64 + fl], acc[c][t][0]);
+      if (acc[c][t][1] != 0.f) atomicAdd(&red[(c * 9 + t) * 64 + fl + 1], acc[c][t][1]);
     }
-    const float s = red[0][threadIdx.x][36] + red[1][threadIdx.x][36] + red[2][threadIdx.x][36] + red[3][threadIdx.x][36];
-    atomicAdd(db + f, s);
+  }
+  atomicAdd(&red[36 * 64 + fl], bs0);
+  atomicAdd(&red[36 * 64 + fl + 1], bs1);
+  __syncthreads();
+  for (int i = threadIdx.x; i < 37 * 64; i += 256) {
+    const int k = i >> 6, fo = blockIdx.y * 64 + (i & 63);
+    const float s = red[i];
+    if (fo >= F || s == 0.f) continue;
+    if (k == 36) atomicAdd(db + fo, s);
+    else if (k < CC * 9) atomicAdd(dw + (static_cast<size_t>(fo) * Cimg + k / 9) * 9 + k % 9, s);
   }
 }
 
@@ -361,12 +394,14 @@ extern "C" int srb_conv_in_bwd(const float* img, int B, int Cimg, int H, int W, 
   cudaMemsetAsync(dw, 0, sizeof(float) * F * Cimg * 9, (cudaStream_t)stream);
   cudaMemsetAsync(db, 0, sizeof(float) * F, (cudaStream_t)stream);
   const long long npix = 1LL * B * H * W;
-  int blocks = 16 * sm_count();                 // the per-thread pixel loop is a chain of dependent loads: keep it short
-  int ppb = ceil_div(npix, blocks); if (ppb < 64) ppb = 64;
-  dim3 grid(ceil_div(npix, ppb), (F + 63) / 64);
-  conv_in_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, Cimg, H, W, multiplier, power,
-                                                             (const __nv_bfloat16*)g, g_cstride, g_coff,
-                                                             (const __nv_bfloat16*)g2, g2_cstride, g2_coff, F, dw, db, ppb);
+  if (F % 2) return set_error("conv_in_bwd: F must be even");
+  const long long warps = 3LL * sm_count() * 8;          // 80 registers per thread (one image channel): 3 blocks per SM
+  int ppw = ceil_div(npix, warps); if (ppw < 16) ppw = 16;
+  dim3 grid(ceil_div(npix, 8LL * ppw), (F + 63) / 64);
+#define SRB_CIB(CC) conv_in_bwd_kernel<CC><<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, Cimg, H, W, multiplier, power, \
+      (const __nv_bfloat16*)g, g_cstride, g_coff, (const __nv_bfloat16*)g2, g2_cstride, g2_coff, F, dw, db, ppw)
+  if (Cimg == 1) SRB_CIB(1); else if (Cimg == 2) SRB_CIB(2); else if (Cimg == 3) SRB_CIB(3); else SRB_CIB(4);
+#undef SRB_CIB
   SRB_LAUNCH_CHECK("conv_in_bwd");
   return 0;
 }

@@ -7,7 +7,11 @@
 //                        image, and their gradient w.r.t. the generated image, in three small kernels.
 //   srb_ragan            esrgan.py:507-508 / 578-588: relativistic-average BCE-with-logits, loss and both gradients.
 //   srb_gp_fwd / _bwd    esrgan.py:604-605: ((||g_b||_2 - 1)^2).mean() * lambda/2 and its gradient.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace srb {
 
@@ -81,19 +85,38 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
 }
 
 // ------------------------------------------------------------------ pixel losses
-// A: per HR pixel p, m[p] = mean_b gen - mean_b gt; accumulates sum |m| into acc[0]
-__global__ void pix_mean_kernel(const float* __restrict__ gen, const float* __restrict__ gt, int B, int HW,
-                                float* __restrict__ msign, float* __restrict__ acc) {
+// A: per HR pixel p, m[p] = mean_b gen - mean_b gt; accumulates sum |m| into acc[0].
+// H W pixels alone are 25 blocks at 80x80: the batch is split over the kPixMeanSplit blocks of a thread-block cluster
+// (each sums its images in order, eight images' loads in flight per thread) and rank 0 adds the partial sums through
+// distributed shared memory in rank order - deterministic, one launch.
+constexpr int kPixMeanSplit = 8;
+__global__ void __cluster_dims__(1, kPixMeanSplit, 1) __launch_bounds__(256)
+pix_mean_kernel(const float* __restrict__ gen, const float* __restrict__ gt, int B, int HW,
+                float* __restrict__ msign, float* __restrict__ acc) {
+  __shared__ float part[256];
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank();
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  float a = 0.f;
+  const int per = (B + kPixMeanSplit - 1) / kPixMeanSplit;
+  const int b0 = rank * per, b1 = min(B, b0 + per);
+  float s = 0.f;
   if (p < HW) {
-    float s = 0.f;
-#pragma unroll 8                                  // same add order, eight images' loads in flight per thread
-    for (int b = 0; b < B; ++b) s += gen[(size_t)b * HW + p] - gt[(size_t)b * HW + p];
+#pragma unroll 8
+    for (int b = b0; b < b1; ++b) s += gen[(size_t)b * HW + p] - gt[(size_t)b * HW + p];
+  }
+  part[threadIdx.x] = s;
+  cluster.sync();
+  float a = 0.f;
+  if (rank == 0 && p < HW) {
+    s = 0.f;
+#pragma unroll
+    for (int r = 0; r < kPixMeanSplit; ++r) s += cluster.map_shared_rank(part, r)[threadIdx.x];
     s /= B;
     msign[p] = s > 0.f ? 1.f : (s < 0.f ? -1.f : 0.f);
     a = fabsf(s);
   }
+  cluster.sync();                                    // the other ranks' shared memory stays alive until rank 0 has read it
+  if (rank != 0) return;
   a = block_sum(a);
   if (threadIdx.x == 0) atomicAdd(acc, a);
 }
@@ -285,7 +308,7 @@ extern "C" int srb_pixel_losses_pow(const float* gen, const float* gt, const flo
   cudaStream_t st = (cudaStream_t)stream;
   const int HW = H * W, h = H / k, w = W / k;
   cudaMemsetAsync(acc, 0, 2 * sizeof(float), st);
-  pix_mean_kernel<<<ceil_div(HW, 256), 256, 0, st>>>(gen, gt, B, HW, msign, acc);
+  pix_mean_kernel<<<dim3(ceil_div(HW, 256), kPixMeanSplit), 256, 0, st>>>(gen, gt, B, HW, msign, acc);
   SRB_CHK("pix_mean");
   pix_lr_kernel<<<ceil_div(1LL * B * h * w, 256), 256, 0, st>>>(gen, lr, B, H, W, k, lr_power, dsign, acc);
   SRB_CHK("pix_lr");

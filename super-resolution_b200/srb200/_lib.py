@@ -15,7 +15,8 @@ import threading
 
 PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(PKG_DIR, "csrc")
-LIB_PATH = os.path.join(PKG_DIR, "libsrb200.so")
+# SRB_LIB_PATH: load another build of the same ABI (A/B timing of kernel changes on one GPU box); never rebuilt here
+LIB_PATH = os.environ.get("SRB_LIB_PATH") or os.path.join(PKG_DIR, "libsrb200.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 
@@ -67,6 +68,8 @@ def sources():
 
 
 def needs_build() -> bool:
+    if os.environ.get("SRB_LIB_PATH"):
+        return False
     if not os.path.exists(LIB_PATH):
         return True
     t = os.path.getmtime(LIB_PATH)
