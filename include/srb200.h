@@ -292,6 +292,24 @@ int srb_mask_loss(const float* gen, const float* gt, long long n, float sigma, f
 int srb_hit_loss(const float* gen, const float* gt, int B, int H, int W, int factor, float thr, float sig, float w,
                  int accumulate, float* work, float* loss, float* grad, void* stream);
 
+/* ---- sorted-Wasserstein / Sinkhorn generator loss term (csrc/sinkhorn.cu; lambda_wasser = 0 in options/default.json) ----
+ * srb_sinkhorn_loss: esrgan.py:539-542 (per-image torch.sort of generated / ground truth, cut_smaller utils.py:241-255,
+ *   SinkhornDistance(opt.sinkhorn_eps, 100, 'sum') utils.py:147-238; constructed at esrgan.py:321).
+ *   gen, truth : fp32 [B][HW] images (HW <= 32768)
+ *   eps, max_iter, thresh : SinkhornDistance's eps, max_iter (100) and stopping threshold (0.1, utils.py:194)
+ *   cap1, cap2 : capacity (points per image) for the generated / true cloud, 12*cap1 + 16*cap2 <= 220 KB; a batch whose
+ *                cut_smaller size exceeds it yields loss = NaN and info[3] = 1 (nothing is added to grad)
+ *   loss       : device scalar, sum over the batch of the transport costs
+ *   grad       : fp32 [B][HW] or NULL; w * d loss / d gen is ADDED into it (through all Sinkhorn iterations, as
+ *                autograd does in the reference)
+ *   info       : device int[4] or NULL: points of the two clouds, iterations run, capacity-overflow flag
+ *   workspace  : srb_sinkhorn_workspace_bytes(...) bytes, 256-byte aligned; holds the duals of every iteration
+ * No host synchronisation: max_iter forward and max_iter backward launches whose CTAs exit at once after convergence. */
+size_t srb_sinkhorn_workspace_bytes(int B, int HW, int cap1, int cap2, int max_iter);
+int srb_sinkhorn_loss(const float* gen, const float* truth, int B, int HW, float eps, int max_iter, float thresh,
+                      int cap1, int cap2, float w, void* workspace, size_t workspace_bytes, float* loss, float* grad,
+                      int* info, void* stream);
+
 /* ---- data path (csrc/data_path.cu) ---------------------------------------------------
  * srb_extract_batch: datasets.py:136-145 (extract) + datasets.py:247-249 / models.py:297-305 (SumPool2d) for a batch.
  *   pairs : fp32 [B][N][2] = (flat index, energy) lists, zero padded (a zero energy ends a list)

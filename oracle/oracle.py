@@ -325,13 +325,57 @@ def kld_hist(q_entries: Tensor, p_entries: Tensor, binedges: Tensor) -> Tensor:
     return F.kl_div(q, p, reduction="sum") / binsizes.mean()
 
 
+def cut_smaller(t: Tensor, threshold: float = 0.0) -> Tensor:
+    """utils.py:241-255: of a row-wise ascending (B, N) tensor keep the last n columns, n = the largest per-row count
+    of entries above ``threshold`` (rows with fewer such entries keep some smaller ones; n == 0 keeps everything, as
+    the reference's ``t[:, -0:]`` does)."""
+    n = int((t > threshold).sum(1).max())
+    return t[:, -n:]
+
+
+def sinkhorn_distance(x: Tensor, y: Tensor, eps: float, max_iter: int = 100, thresh: float = 0.1
+                      ) -> Tuple[Tensor, int]:
+    """SinkhornDistance(eps, max_iter, 'sum').forward (utils.py:176-219) for point clouds x (B, P1, 1), y (B, P2, 1)
+    with uniform marginals: cost C = |x_i - y_j|^2 (228-234), log-domain updates of the duals u, v (198-199) until
+    the batch mean of sum_i |u - u_prev| drops below 0.1 (200-204), then sum_b sum_ij pi_ij C_ij with
+    pi = exp((-C + u_i + v_j) / eps) (206-216).  Returns (cost, iterations run)."""
+    C = ((x.unsqueeze(-2) - y.unsqueeze(-3)).abs() ** 2).sum(-1)
+    B, P1, P2 = C.shape
+    log_mu = torch.log(torch.full((B, P1), 1.0 / P1) + 1e-8)
+    log_nu = torch.log(torch.full((B, P2), 1.0 / P2) + 1e-8)
+    u, v = torch.zeros(B, P1), torch.zeros(B, P2)
+
+    def m(u_, v_):                                                    # utils.py:221-224
+        return (-C + u_.unsqueeze(-1) + v_.unsqueeze(-2)) / eps
+
+    nits = 0
+    for _ in range(max_iter):
+        u_prev = u
+        u = eps * (log_mu - torch.logsumexp(m(u, v), -1)) + u
+        v = eps * (log_nu - torch.logsumexp(m(u, v).transpose(-2, -1), -1)) + v
+        nits += 1
+        if (u - u_prev).abs().sum(-1).mean().item() < thresh:
+            break
+    pi = torch.exp(m(u, v))
+    return (pi * C).sum((-2, -1)).sum(), nits
+
+
+def wasserstein_loss(gen: Tensor, truth: Tensor, eps: float) -> Tensor:
+    """esrgan.py:539-542: Sinkhorn distance between the per-image sorted pixel values of the generated and the true
+    image, each cut to the largest non-zero count of its batch."""
+    B = gen.shape[0]
+    gen_sort = torch.sort(gen.reshape(B, -1), 1)[0]
+    real_sort = torch.sort(truth.reshape(B, -1), 1)[0]
+    return sinkhorn_distance(cut_smaller(gen_sort)[..., None], cut_smaller(real_sort)[..., None], eps)[0]
+
+
 def generator_loss(gen: Sequence[Tensor], hr: Tensor, lr: Tensor, d_sds: Sequence[SD], *, factor: int,
                    scaling_power: float = 1.0, lambdas=(0.2, 1.0), lambda_hr=1.0, lambda_lr=0.1,
                    lambda_adv=0.01, lambda_nnz=0.0, lambda_mask=0.0, lambda_hist=0.0, lambda_hit=0.0,
-                   binedges: Optional[Sequence[Tensor]] = None, sigma: float = 500, hit_threshold: float = 0.5
-                   ) -> Tuple[Tensor, Dict[str, Tensor]]:
+                   binedges: Optional[Sequence[Tensor]] = None, sigma: float = 500, hit_threshold: float = 0.5,
+                   lambda_wasser: float = 0.0, sinkhorn_eps: float = 0.1) -> Tuple[Tensor, Dict[str, Tensor]]:
     """G-step loss assembly, esrgan.py:468-552 with the default.json weights (+ the optional nnz / mask / hist / hit
-    terms of 530-550 when their lambda is > 0).  ``gen`` = (generator output, generator.srs)."""
+    / wasser terms of 530-550 when their lambda is > 0).  ``gen`` = (generator output, generator.srs)."""
     ground_truth = (hr, hr ** scaling_power)                                  # 470
     gen_lr = sum_pool(gen[0], factor)                                         # 471
     generated_lr = (gen_lr, gen_lr ** scaling_power)                          # 472
@@ -360,6 +404,9 @@ def generator_loss(gen: Sequence[Tensor], hr: Tensor, lr: Tensor, d_sds: Sequenc
             real_hist = diffable_histogram(ground_truth[k][ground_truth[k] > 0], binedges[k], sigma)
             parts[f"hist{k}"] = kld_hist(gen_hist, real_hist, binedges[k])
             tot = tot + lambda_hist * parts[f"hist{k}"]
+        if lambda_wasser > 0:                                                   # 539-542
+            parts[f"wasser{k}"] = wasserstein_loss(gen[k], ground_truth[k], sinkhorn_eps)
+            tot = tot + lambda_wasser * parts[f"wasser{k}"]
         if lambda_hit > 0:                                                      # 546-550
             parts[f"hit{k}"] = F.mse_loss(get_hitogram(gen[k], factor, hit_threshold, sigma),
                                           get_hitogram(ground_truth[k], factor, hit_threshold, sigma))

@@ -7,8 +7,8 @@
 //                            factor x factor cells
 // Each is a fused reduction that also produces d loss / d generated (added into the generator step's gradient image),
 // so none of them builds an autograd graph or materialises the [bins x pixels] tensor the reference's histogram does.
-// HBM-bound: one or two reads of the batch.  (The sorted-Wasserstein / Sinkhorn term of esrgan.py:539-542 is not built:
-// its gradient runs through up to 100 autograd-unrolled Sinkhorn iterations with a host-side early exit.)
+// HBM-bound: one or two reads of the batch.  (The sorted-Wasserstein / Sinkhorn term of esrgan.py:539-542 lives in
+// csrc/sinkhorn.cu.)
 #include "common.cuh"
 
 namespace srb {

@@ -23,6 +23,7 @@
 #include "disc_mma.cu"
 #include "optim_loss.cu"
 #include "opt_losses.cu"
+#include "sinkhorn.cu"
 #include "data_path.cu"
 #include "eval_stats.cu"
 #include "api.cu"

@@ -182,3 +182,35 @@ def hist_loss(gen, gt, k, sigma, w, grad, work: OptionalLossWork):
     L.check(lib.srb_soft_hist_bwd(g.data_ptr(), g.numel(), b["centers"].data_ptr(), b["deltas"].data_ptr(), b["n"],
                                   float(sigma), b["dq"].data_ptr(), float(w), 1, grad.data_ptr(), _st()), "soft_hist_bwd")
     return loss
+
+
+class SinkhornWork:
+    """Workspace of srb_sinkhorn_loss for one (B, H*W): sorted values, the duals of every iteration, adjoints."""
+
+    def __init__(self, B, HW, dev, max_iter=100, cap1=None, cap2=None):
+        if cap1 is None:
+            cap1 = min(HW, 12288)
+        if cap2 is None:
+            cap2 = min(HW, (220 * 1024 - 12 * cap1) // 16)
+        self.B, self.HW, self.max_iter, self.cap1, self.cap2 = B, HW, int(max_iter), int(cap1), int(cap2)
+        n = L.lib().srb_sinkhorn_workspace_bytes(B, HW, self.cap1, self.cap2, self.max_iter)
+        if n == 0:
+            raise RuntimeError("CUDA srb200: bad Sinkhorn workspace arguments")
+        self.ws = torch.empty(n, dtype=torch.uint8, device=dev)
+        self.info = torch.zeros(4, dtype=torch.int32, device=dev)
+
+
+def wasserstein_loss(gen, gt, eps, w, grad, work: SinkhornWork, thresh=0.1):
+    """esrgan.py:539-542: SinkhornDistance(eps, 100, 'sum') between the per-image sorted pixel values, cut to the
+    batch's largest positive count; adds w * d loss / d gen into ``grad`` (None: value only).  ``work.info`` then holds
+    (points generated, points true, iterations run, capacity overflow)."""
+    g, t = _c(gen), _c(gt)
+    B = g.shape[0]
+    HW = g[0].numel()
+    assert (B, HW) == (work.B, work.HW)
+    loss = torch.empty((), device=g.device)
+    L.check(L.lib().srb_sinkhorn_loss(g.data_ptr(), t.data_ptr(), B, HW, float(eps), work.max_iter, float(thresh),
+                                      work.cap1, work.cap2, float(w), work.ws.data_ptr(), work.ws.numel(),
+                                      loss.data_ptr(), grad.data_ptr() if grad is not None else None,
+                                      work.info.data_ptr(), _st()), "sinkhorn_loss")
+    return loss

@@ -37,7 +37,7 @@ class GANTrainStep:
                  betas=(0.9, 0.999), l2decay=0.0, scaling_power=1.0, process_group=None, use_disc_engine=True,
                  second_discriminators: Optional[Sequence] = None, second_discr_reset_interval: int = 0,
                  uniform_reset: bool = False, lambda_nnz=0.0, lambda_mask=0.0, lambda_hist=0.0, lambda_hit=0.0,
-                 binedges=None, sigma=500.0, hit_threshold=0.5):
+                 binedges=None, sigma=500.0, hit_threshold=0.5, lambda_wasser=0.0, sinkhorn_eps=0.1):
         """``scaling_power``: opt.scaling_power (esrgan.py:470-473): the "pow" branch (k = 1) compares generator.srs with
         hr ** p, the pooled image ** p with lr ** p, and shows D_pow the powered images; the generator must have been
         built with power=p.  ``second_discriminators``: the SecondDiscriminators ensemble of esrgan.py:221-237 (one per
@@ -46,9 +46,10 @@ class GANTrainStep:
         re-initialised every ``second_discr_reset_interval`` iterations (789-795).
         ``lambda_nnz / lambda_mask / lambda_hist / lambda_hit``: the optional terms of esrgan.py:530-550 on fused kernels
         (csrc/opt_losses.cu); ``binedges`` = per branch the histogram bin edges esrgan.py:440-450 derives during warm-up
-        (info['binedges0'], info['binedges1']), ``sigma`` = opt.sigma, ``hit_threshold`` = opt.hit_threshold.  The
-        sorted-Wasserstein / Sinkhorn term (lambda_wasser, esrgan.py:539-542) is not part of the fused step."""
+        (info['binedges0'], info['binedges1']), ``sigma`` = opt.sigma, ``hit_threshold`` = opt.hit_threshold.
+        ``lambda_wasser`` / ``sinkhorn_eps``: the sorted-Wasserstein / Sinkhorn term of esrgan.py:539-542 (csrc/sinkhorn.cu)."""
         self.l_nnz, self.l_mask, self.l_hist, self.l_hit = lambda_nnz, lambda_mask, lambda_hist, lambda_hit
+        self.l_wasser, self.sinkhorn_eps = float(lambda_wasser), float(sinkhorn_eps)
         self.binedges, self.sigma, self.hit_threshold = binedges, float(sigma), float(hit_threshold)
         if lambda_hist > 0 and binedges is None:
             raise RuntimeError("CUDA srb200: lambda_hist > 0 needs the bin edges (esrgan.py:440-450)")
@@ -135,7 +136,8 @@ class GANTrainStep:
         if w is None:
             w = dict(w0=LS.PixelLossWork(B, H, W, self.factor, dev), w1=LS.PixelLossWork(B, H, W, self.factor, dev),
                      g0=torch.empty(B, 1, H, W, device=dev), g1=torch.empty(B, 1, H, W, device=dev),
-                     opt=LS.OptionalLossWork(B, H, W, self.factor, dev, self.binedges))
+                     opt=LS.OptionalLossWork(B, H, W, self.factor, dev, self.binedges),
+                     sink=LS.SinkhornWork(B, H * W, dev) if self.l_wasser > 0 else None)
             self._work[key] = w
         return w
 
@@ -191,6 +193,8 @@ class GANTrainStep:
                     ("nnz", self.l_nnz, lambda c: LS.nnz_loss(generated[k], truth[k], c, g[k], wk["opt"])),
                     ("mask", self.l_mask, lambda c: LS.mask_loss(generated[k], truth[k], c, g[k])),
                     ("hist", self.l_hist, lambda c: LS.hist_loss(generated[k], truth[k], k, self.sigma, c, g[k], wk["opt"])),
+                    ("wasser", self.l_wasser, lambda c: LS.wasserstein_loss(generated[k], truth[k], self.sinkhorn_eps, c,
+                                                                            g[k], wk["sink"])),
                     ("hit", self.l_hit, lambda c: LS.hit_loss(generated[k], truth[k], self.factor, self.hit_threshold,
                                                               self.sigma, c, g[k], wk["opt"]))):
                 if coef > 0:
