@@ -59,4 +59,11 @@ int dmma_conv_pitched(const void* in_bf16, const float* in_f32, int cin, const v
 int dmma_wgrad_pitched(const void* gz_bf16, const float* gz_f32, int cout, const void* a_bf16, int cin, float* dw,
                        float* db, int B, int Hi, int Wi, int Hip, int Wip, int Ho, int Wo, int stride, void* stream);
 
+// csrc/conv_out_tc.cu: conv3.2 (64 -> 1 channel) forward + head and its fused backward, taps folded into the GEMM.
+// c32_fwd_launch returns -1 when the geometry does not fit (the caller keeps the general path).
+int c32_fwd_launch(const void* x, int B, int H, int W, const float* w, const float* bias, float inv_multiplier,
+                   float power, float thres, int training, float* out, float* srs, float* z, cudaStream_t st);
+int c32_bwd_launch(const float* gz, const float* w, const void* act, void* gy, float* dw, float* db, int B, int H, int W,
+                   float slope, cudaStream_t st);
+
 }  // namespace srb

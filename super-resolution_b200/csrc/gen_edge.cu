@@ -6,6 +6,8 @@
 //             pre-head value z (kept for backward).
 //   Their backward kernels, and the PixelShuffle adjoint ("unshuffle") used by the upsampling backward.
 // All are CUDA-core kernels: K = 9*channels or N = channels (1 by default) cannot feed a tensor core.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "sm100.cuh"
 
@@ -441,6 +443,13 @@ __global__ void head_fwd_kernel(float* __restrict__ out, float* __restrict__ srs
   out[i] = hardshrink(o2, thres);
 }
 
+// SRB_CONV_OUT_GENERAL=1: conv3.2 on the general warp-MMA kernels of disc_mma.cu (one product per tap) - the round-1 path,
+// kept for A/B timing and as the fall-back for geometries conv_out_tc.cu does not take
+static bool conv_out_general_path() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("SRB_CONV_OUT_GENERAL"); v = (e && atoi(e) != 0) ? 1 : 0; }
+  return v == 1;
+}
 static bool conv_out_tc_ok(int Cimg, int F, int cstride, int coff, int W) {
   return Cimg == 1 && F == 64 && cstride == 64 && coff == 0 && W >= 8;
 }
@@ -452,6 +461,10 @@ extern "C" int srb_conv_out_fwd(const void* x, int x_cstride, int x_coff, int B,
   if ((x_cstride % 8) || (x_coff % 8)) return set_error("conv_out: channel stride/offset must keep 16-byte alignment");
   if (conv_out_tc_ok(Cimg, F, x_cstride, x_coff, W)) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (!conv_out_general_path()) {          // taps-in-the-GEMM kernel with the output head fused (csrc/conv_out_tc.cu)
+      const int rc = c32_fwd_launch(x, B, H, W, w, bias, 1.f / multiplier, power, thres, training, out, srs, z, st);
+      if (rc >= 0) return rc;
+    }
     conv_out_pack_kernel<<<8, 256, 0, st>>>(w);
     SRB_LAUNCH_CHECK("conv_out_pack");
     void* wp = nullptr;
@@ -484,6 +497,11 @@ extern "C" int srb_conv_out_bwd(const float* z, const float* g_out, const float*
                                                     gz_scratch);
   SRB_LAUNCH_CHECK("head_bwd");
   if (conv_out_tc_ok(Cimg, F, act_cstride, act_coff, W) && gy_cstride == 64 && gy_coff == 0) {
+    if (!conv_out_general_path()) {          // input gradient + weight gradient in one pass over the activations
+      cudaMemsetAsync(dw, 0, sizeof(float) * F * 9, st);
+      cudaMemsetAsync(db, 0, sizeof(float), st);
+      return c32_bwd_launch(gz_scratch, w, act, gy, dw, db, B, H, W, slope, st);
+    }
     conv_out_pack_kernel<<<8, 256, 0, st>>>(w);
     SRB_LAUNCH_CHECK("conv_out_pack");
     void* wp = nullptr;

@@ -21,6 +21,7 @@
 #include "disc_fast.cu"
 #include "disc.cu"
 #include "disc_mma.cu"
+#include "conv_out_tc.cu"
 #include "optim_loss.cu"
 #include "opt_losses.cu"
 #include "sinkhorn.cu"

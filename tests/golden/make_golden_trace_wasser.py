@@ -14,7 +14,7 @@ import ref_harness  # noqa: E402
 
 if __name__ == "__main__":
     r = ref_harness.run("/root/reference", None, n_batches=6, batch_size=4, seed=977, factor=4, residual_blocks=1,
-                        overrides=dict(lambda_wasser=0.05))
+                        overrides=dict(lambda_wasser=0.002))
     r.pop("stdout_tail")
     r.pop("step_t", None)
     r["models_file"] = "reference models.py"
