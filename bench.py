@@ -362,6 +362,7 @@ def run_ours(args):
         c0 = L.CALLS[0]
         t0 = time.perf_counter()
         graphed = GraphedStep(trainer, lr, hr, warmup=2)       # 2 eager steps + 1 captured
+        _GRAPHS.append(graphed.graph)
         torch.cuda.synchronize()
         t_capture = time.perf_counter() - t0
         calls_per_step = (L.CALLS[0] - c0) // 3
@@ -512,6 +513,7 @@ def run_ours(args):
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
             g_graph = torch.cuda.CUDAGraph()
+            _GRAPHS.append(g_graph)
             with torch.cuda.graph(g_graph):
                 gts.step(lr, hr)
             g_step = g_graph.replay
@@ -593,21 +595,37 @@ def run_ours(args):
     finish(world)
 
 
+_GRAPHS = []        # every CUDA graph this process captured (they hold NCCL kernels when world > 1)
+
+
 def finish(world):
-    if world > 1:
-        import torch.distributed as dist
-        # The captured graphs hold NCCL kernels; destroying the communicator while a graph that references it is alive
-        # hung in round 1.  Everything is printed; make sure all ranks are done, drop python references to the graphs,
-        # then tear down in order.  (os._exit stays as the fallback if the teardown stalls: SRB_BENCH_HARD_EXIT=1.)
-        dist.barrier()
-        torch.cuda.synchronize()
-        sys.stdout.flush()
-        sys.stderr.flush()
-        if os.environ.get("SRB_BENCH_HARD_EXIT", "1") == "1":
-            os._exit(0)
-        import gc
-        gc.collect()
-        dist.destroy_process_group()
+    """Orderly multi-rank teardown.  destroy_process_group() hung in round 1 while captured graphs that contain NCCL
+    kernels were still alive: release the graphs' device resources first (CUDAGraph.reset()), synchronise, meet at a
+    barrier, then destroy the communicator.  A watchdog keeps the old hard exit as the fallback, so that a stalled
+    teardown can never hold the node (everything has been printed and flushed by then)."""
+    if world <= 1:
+        return
+    import threading
+    import torch.distributed as dist
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    if os.environ.get("SRB_BENCH_HARD_EXIT", "0") == "1":
+        os._exit(0)
+    timer = threading.Timer(float(os.environ.get("SRB_BENCH_TEARDOWN_S", "20")), lambda: os._exit(0))
+    timer.daemon = True
+    timer.start()
+    for g in _GRAPHS:
+        g.reset()
+    del _GRAPHS[:]
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
+    dist.destroy_process_group()
+    timer.cancel()
+    print("teardown: process group destroyed", file=sys.stderr, flush=True)
 
 
 # ----------------------------------------------------------------------------------------------- hyper-search sweep
@@ -645,6 +663,7 @@ def run_sweep(args, dev, world, rank, pg, barrier):
             t_build = time.perf_counter() - t0
             t0 = time.perf_counter()
             graphed = GraphedStep(trainer, lr, hr, warmup=2)
+            _GRAPHS.append(graphed.graph)
             torch.cuda.synchronize()
             t_cap = time.perf_counter() - t0
             ms = timed(lambda: graphed.step(lr, hr), max(3, min(args.steps, 10)), 2, barrier)

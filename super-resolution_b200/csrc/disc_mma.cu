@@ -196,6 +196,27 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
       }
       const int hi = lane >> 4;
       const bool two = (pr * 2 + 1) < nfrag;
+      // destination pixel of staging row `lane` of the epilogue (-1: nothing to store).  It does not depend on the
+      // accumulators: with the mask epilogue its reference row goes to L1 now, behind the MMAs, instead of being a
+      // ~1 us dependent load after them (these layers are latency-bound: 16 warps per SM).
+      int mypix = -1;
+      if constexpr (NT >= 2) {
+        const int m = pr * 32 + lane;
+        if (m < M && (lane < 16 || two)) {
+          const int im = __umulhi(m, p.mg_img);
+          const int rem = m - im * M_img;
+          const int yl = __umulhi(rem, p.mg_w), x = rem - yl * Wg;
+          const int b = img0 + im, yg = y0 + yl;
+          if (b < p.B && yg < Hg) {
+            const int yd = MODE == 0 ? yg : 2 * yg + py;
+            const int xd = MODE == 0 ? x : 2 * x + px;
+            mypix = (b * p.Hdp + yd) * p.Wdp + xd;
+          }
+        }
+        if (p.act == 2 && mypix >= 0)
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const uint4*>(p.ref) +
+                                                        static_cast<size_t>(static_cast<uint32_t>(mypix)) * NT));
+      }
       const uint32_t wlane = dsmem_u32(w_s) + ((lane & 7) + ((lane >> 4) << 3)) * PP + ((lane >> 3) & 1) * 16;
       const uint32_t wlane2 = dsmem_u32(w_s) + (lane & 7) * PP + ((lane >> 3) & 1) * 16;   // x2 form (NT == 1)
 #pragma unroll
@@ -246,22 +267,6 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
         constexpr int SP = NT * 16 + 16;
         constexpr int RPI = 32 / NT;                  // staging rows covered by the warp per 16-byte pass
         const uint32_t stg = dsmem_u32(stage_s) + warp * (32 * SP);
-        // destination pixel of staging row `lane` (-1: nothing to store)
-        int mypix = -1;
-        {
-          const int m = pr * 32 + lane;
-          if (m < M && (lane < 16 || two)) {
-            const int im = __umulhi(m, p.mg_img);
-            const int rem = m - im * M_img;
-            const int yl = __umulhi(rem, p.mg_w), x = rem - yl * Wg;
-            const int b = img0 + im, yg = y0 + yl;
-            if (b < p.B && yg < Hg) {
-              const int yd = MODE == 0 ? yg : 2 * yg + py;
-              const int xd = MODE == 0 ? x : 2 * x + px;
-              mypix = (b * p.Hdp + yd) * p.Wdp + xd;
-            }
-          }
-        }
         if (p.act == 1) {                             // LeakyReLU, slope in (0, 1): max(v, slope * v)
 #pragma unroll
           for (int f = 0; f < 2; ++f)
