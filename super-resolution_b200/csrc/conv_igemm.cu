@@ -78,6 +78,13 @@ __device__ __forceinline__ void load_row64(const __nv_bfloat16* p, uint4 (&v)[8]
 // kernel (conv_chain.cu) reads rows that an earlier layer of the SAME launch wrote.
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
+// Sign words: row-major [pixel][cstride words] (cstride > 0) or plane-major [word][-cstride pixels] (cstride < 0).
+// Plane-major makes a warp's 32 rows x one word a single 128-byte access instead of 32 sectors with 4 useful bytes.
+__device__ __forceinline__ size_t sign_word_index(int q, int cstride, int word) {
+  return cstride >= 0 ? static_cast<size_t>(q) * cstride + word
+                      : static_cast<size_t>(word) * static_cast<size_t>(-cstride) + q;
+}
+
 // The LeakyReLU' mask rows of a tile do not depend on its accumulators: pull them into L2 before waiting for the MMAs
 // (they are forward activations, long evicted by the time the input-gradient pass reads them).
 template <int MT>
@@ -87,7 +94,7 @@ __device__ __forceinline__ void igemm_prefetch_mask(const IgemmParams& p, int mt
   for (int mt = 0; mt < MT; ++mt) {
     const int q = mt_idx * (128 * MT) + mt * 128 + lg * 32 + lane;
     if (q >= p.R) continue;
-    if (p.mask_bits) prefetch_l2(p.mask_bits + static_cast<size_t>(q) * p.maskb_cstride + p.maskb_coff + nt * 2 + half);
+    if (p.mask_bits) prefetch_l2(p.mask_bits + sign_word_index(q, p.maskb_cstride, p.maskb_coff + nt * 2 + half));
     else prefetch_l2(p.mask + static_cast<size_t>(q) * p.mask_cstride + p.mask_coff + nt * 64 + half * 32);
   }
 }
@@ -208,7 +215,7 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = v[i] > 0.f ? v[i] : v[i] * p.slope;
   } else if (p.act == SRB_ACT_LRELU_MASK && p.mask_bits) {
-    const uint32_t* wp = p.mask_bits + static_cast<size_t>(q) * p.maskb_cstride + p.maskb_coff + (c0 >> 5);
+    const uint32_t* wp = p.mask_bits + sign_word_index(q, p.maskb_cstride, p.maskb_coff + (c0 >> 5));
     const uint32_t bits = COHERENT ? __ldcg(wp) : __ldg(wp);
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] *= ((bits >> i) & 1u) ? 1.f : p.slope;
@@ -230,7 +237,7 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
     uint32_t bits = 0;
 #pragma unroll
     for (int i = 0; i < 32; ++i) bits |= (v[i] > 0.f ? 1u : 0u) << i;
-    p.sign_out[static_cast<size_t>(q) * p.sign_cstride + p.sign_coff + (c0 >> 5)] = bits;
+    p.sign_out[sign_word_index(q, p.sign_cstride, p.sign_coff + (c0 >> 5))] = bits;
   }
   if (EXT && p.y32) {
     float4* y4 = reinterpret_cast<float4*>(p.y32 + static_cast<size_t>(q) * p.y32_cstride + p.y32_coff + c0);

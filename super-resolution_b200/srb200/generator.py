@@ -293,8 +293,9 @@ class GeneratorEngine:
             T.csum = torch.zeros(3, 5 * F_, device=dev)      # per-channel sums of the G buffers (bias gradients)
             # LeakyReLU sign bits of slots 1..4 of every dense block (F = 64: two 32-bit words per slot and pixel),
             # written by the forward convolutions and read by the input-gradient pass instead of the bf16 activations
-            T.sign = [torch.zeros(B, h + 1, w + 1, 8, dtype=torch.int32, device=dev) for _ in range(3 * nb)] \
-                if F_ == 64 else None
+            # plane-major [word][pixel]: a warp's 32 rows of one word are one 128-byte access (SRB_SIGN_ROWMAJOR=1: [pixel][word])
+            shape = (B, h + 1, w + 1, 8) if os.environ.get("SRB_SIGN_ROWMAJOR") == "1" else (8, B * (h + 1) * (w + 1))
+            T.sign = [torch.zeros(*shape, dtype=torch.int32, device=dev) for _ in range(3 * nb)] if F_ == 64 else None
             if self.drop_rate > 0:                           # unmasked copies of the dense blocks' output gradients
                 T.Gu = [ops.pnhwc_zeros(B, h, w, F_, dev) for _ in range(3)]
 

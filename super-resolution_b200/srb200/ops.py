@@ -136,12 +136,17 @@ def conv3x3_args(x: Tensor, x_coff: int, cin: int, wp: Tensor, bias: Optional[Te
         assert chan_scale.dtype == torch.float32 and tuple(chan_scale.shape) == (B, cout) and chan_scale.is_contiguous()
         a.chan_scale = chan_scale.data_ptr()
     a.impl, a.flags = impl, flags
-    if sign_out is not None:    # (int32 [B, H+1, W+1, words], first word): (output > 0) bits, 32 channels per word
-        assert sign_out[0].dtype == torch.int32 and sign_out[0].shape[:3] == y.shape[:3]
-        a.sign_out, a.sign_cstride, a.sign_coff = sign_out[0].data_ptr(), sign_out[0].shape[-1], sign_out[1]
+    def sign_layout(t):         # row-major [B, H+1, W+1, words] -> +words; plane-major [words, B*(H+1)*(W+1)] -> -pixels
+        assert t.dtype == torch.int32 and t.is_contiguous()
+        if t.dim() == 2:
+            assert t.shape[1] == y.shape[0] * y.shape[1] * y.shape[2]
+            return -t.shape[1]
+        assert t.shape[:3] == y.shape[:3]
+        return t.shape[-1]
+    if sign_out is not None:    # (int32 sign words, first word): (output > 0) bits, 32 channels per word
+        a.sign_out, a.sign_cstride, a.sign_coff = sign_out[0].data_ptr(), sign_layout(sign_out[0]), sign_out[1]
     if mask_bits is not None:   # LeakyReLU' from such sign words instead of the bf16 activation
-        assert mask_bits[0].dtype == torch.int32 and mask_bits[0].shape[:3] == y.shape[:3]
-        a.mask_bits, a.maskb_cstride, a.maskb_coff = mask_bits[0].data_ptr(), mask_bits[0].shape[-1], mask_bits[1]
+        a.mask_bits, a.maskb_cstride, a.maskb_coff = mask_bits[0].data_ptr(), sign_layout(mask_bits[0]), mask_bits[1]
     if colsum is not None:      # fp32 [cout] accumulator of per-channel output sums (bias gradient), cout == 64
         assert colsum.dtype == torch.float32 and colsum.numel() >= cout and colsum.is_contiguous()
         a.colsum = colsum.data_ptr()
