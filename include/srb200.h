@@ -78,9 +78,11 @@ typedef struct srb_conv3x3_args {
                                   bit (channel % 32) = (stored output > 0).  Written next to a LeakyReLU output so that
                                   the input-gradient pass can read LeakyReLU' from 1 bit per element (mask_bits)
                                   instead of re-reading the bf16 activation. */
-  int sign_cstride, sign_coff;
-  const void* mask_bits;       /* SRB_ACT_LRELU_MASK: if set, the mask comes from these sign words (same layout) and
-                                  `mask` is ignored */
+  int sign_cstride, sign_coff; /* sign_cstride > 0: row-major, word index = pixel * sign_cstride + word;
+                                  sign_cstride < 0: plane-major uint32 [words][-sign_cstride pixels], word index =
+                                  word * (-sign_cstride) + pixel (32 consecutive pixels of one word = one 128-byte access) */
+  const void* mask_bits;       /* SRB_ACT_LRELU_MASK: if set, the mask comes from these sign words (same layouts, selected by
+                                  the sign of maskb_cstride) and `mask` is ignored */
   int maskb_cstride, maskb_coff;
   float* colsum;               /* optional fp32 [64] (cout == 64 only): += sum over valid pixels of the stored outputs,
                                   per channel, with atomics - the bias gradient of the convolution whose pre-activation
