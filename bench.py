@@ -86,17 +86,21 @@ def traffic_from_profile():
     best = None
     for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_conv3x3_chain*.txt"))):
         txt = open(f).read()
-        rd = re.search(r"dram__bytes_read\.sum\s+\S*\s*([0-9.,]+)\s*(\w?byte)?", txt)
-        wr = re.search(r"dram__bytes_write\.sum\s+\S*\s*([0-9.,]+)", txt)
         m = re.search(r"traffic_bytes_per_launch\s*[:=]\s*([0-9.eE+]+)", txt)
         if m:
             best = (float(m.group(1)), os.path.relpath(f, ROOT))
-        elif rd and wr:
-            unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-            um = re.search(r"dram__bytes_read\.sum\s+(\w+)", txt)
-            k = unit.get(um.group(1), 1.0) if um else 1.0
-            best = ((float(rd.group(1).replace(",", "")) + float(wr.group(1).replace(",", ""))) * k,
-                    os.path.relpath(f, ROOT))
+            continue
+        unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        vals = {}
+        for key in ("read", "write"):       # "<name> [unit]: v | v ..." (r01 files) or "<name>   v unit" (ncu raw page rows)
+            a = re.search(r"dram__bytes_%s\.sum\s*\[(\w+)\]\s*:\s*([0-9.,]+)" % key, txt)
+            b = re.search(r"dram__bytes_%s\.sum\s+([0-9.,]+)\s+(\w+)" % key, txt)
+            if a:
+                vals[key] = float(a.group(2).replace(",", "")) * unit.get(a.group(1), 1.0)
+            elif b:
+                vals[key] = float(b.group(1).replace(",", "")) * unit.get(b.group(2), 1.0)
+        if len(vals) == 2:
+            best = (vals["read"] + vals["write"], os.path.relpath(f, ROOT))
     return best
 
 

@@ -29,9 +29,18 @@ bias = [torch.zeros(F_, device=dev) for _ in range(5)]
 st = lambda: torch.cuda.current_stream().cuda_stream
 
 
+SIGN = os.environ.get("SIGN", "0")      # 0: no sign words; row: [pixel][8]; plane: [8][pixel]
+signs = None
+if SIGN == "row":
+    signs = [torch.zeros(B, H + 1, W + 1, 8, dtype=torch.int32, device=dev) for _ in range(NBLK)]
+elif SIGN == "plane":
+    signs = [torch.zeros(8, B * (H + 1) * (W + 1), dtype=torch.int32, device=dev) for _ in range(NBLK)]
+
+
 def fwd_layers(i):
     cur, nxt = bufs[i], bufs[i + 1]
-    ls = [ops.conv3x3_args(cur, 0, k * F_, packs[k - 1], bias[k - 1], cur, k * F_, F_, act=L.ACT_LRELU, slope=0.01)
+    ls = [ops.conv3x3_args(cur, 0, k * F_, packs[k - 1], bias[k - 1], cur, k * F_, F_, act=L.ACT_LRELU, slope=0.01,
+                           sign_out=(signs[i], 2 * (k - 1)) if signs is not None else None)
           for k in range(1, 5)]
     ls.append(ops.conv3x3_args(cur, 0, 5 * F_, packs[4], bias[4], nxt, 0, F_, alpha=0.2, res1=(cur, 0, 1.0)))
     return ls
