@@ -63,6 +63,8 @@ int dmma_wgrad_pitched(const void* gz_bf16, const float* gz_f32, int cout, const
 // c32_fwd_launch returns -1 when the geometry does not fit (the caller keeps the general path).
 int c32_fwd_launch(const void* x, int B, int H, int W, const float* w, const float* bias, float inv_multiplier,
                    float power, float thres, int training, float* out, float* srs, float* z, cudaStream_t st);
+// discriminator image end, input gradient (dl1_dgrad) on the tap-partial scheme; -1: geometry not covered
+int d16_dgrad_launch(const void* gz, const float* w, float* gx, int C, int B, int H, int W, cudaStream_t st);
 int c32_bwd_launch(const float* gz, const float* w, const void* act, void* gy, float* dw, float* db, int B, int H, int W,
                    float slope, cudaStream_t st);
 

@@ -310,6 +310,161 @@ c32_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const C32BwdP p) {
   }
 }
 
+// ---------------------------------------------------------------- image end of the discriminator: input gradient
+// gx[p] = sum_t sum_c gz[p - s_t][c] w[c][t]   (models.py:142 for in_filters = 1; esrgan.py:494-508 through the generator's
+// adversarial term and 602 for the gradient penalty): the same tap-partial scheme as c32_fwd_kernel over UNPADDED bf16
+// NHWC [B][H][W][C] rows (C = 16 KS channels): d[q][t] = sum_c gz[q][c] w[c][t], then the nine planes are gathered with
+// explicit border tests.  The fp32 weights enter as bf16 hi + lo (two k-steps per 16 channels against the same A
+// fragment), so the products keep ~2^-17 relative accuracy like the CUDA-core kernel this replaces.
+struct D16DgradP {
+  const float* w;                          // fp32 [C][1][3][3]
+  float* gx;                               // fp32 [B][H][W]
+  int B, H, W, blocks_per_img, n_tiles, tr_max;
+};
+
+template <int KS>
+__global__ void __launch_bounds__(kC32Threads, 2)
+d16_dgrad_kernel(const __grid_constant__ CUtensorMap tmap, const D16DgradP p) {
+  constexpr int C = KS * 16, P = KS * 32;               // channels, bytes per pixel row
+  constexpr int SH = KS == 1 ? 2 : KS == 2 ? 1 : 0, SWM = 2 * KS - 1;      // TMA swizzle of a P-byte row (disc_mma.cu)
+  constexpr int kStages = 4;
+  constexpr int RPB = 16;                               // pixel rows per TMA box (larger boxes cost resident CTAs: measured slower)
+  constexpr int kSlot = RPB * P;
+  extern __shared__ __align__(1024) uint8_t c32_smem[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(c32_smem) + 1023) & ~uintptr_t(1023));
+  uint8_t* ring = base;                                                            // [warp][stage][kSlot]
+  __nv_bfloat16* w_s = reinterpret_cast<__nv_bfloat16*>(ring + kC32Warps * kStages * kSlot);   // [2 (hi, lo)][16 taps][C]
+  float* ds = reinterpret_cast<float*>(w_s + 2 * 16 * C);                          // [9][tr_max]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ds + 9 * p.tr_max);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  for (int i = threadIdx.x; i < 16 * C; i += kC32Threads) {
+    const int t = i / C, c = i - t * C;
+    const float v = t < 9 ? p.w[c * 9 + t] : 0.f;
+    const __nv_bfloat16 hi = __float2bfloat16(v);
+    w_s[i] = hi;
+    w_s[16 * C + i] = __float2bfloat16(v - __bfloat162float(hi));
+  }
+  if (lane == 0) {
+    if (warp == 0) tma_prefetch_desc(&tmap);
+    for (int s = 0; s < kStages; ++s) mbar_init(&bars[warp * kStages + s], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  uint32_t wb[2][KS][4];                                 // [hi | lo][k-step][b0 nt0, b1 nt0, b0 nt1, b1 nt1]
+#pragma unroll
+  for (int h = 0; h < 2; ++h)
+#pragma unroll
+    for (int kk = 0; kk < KS; ++kk)
+      ldsm_x4(smem_u32(w_s + h * 16 * C) + ((lane & 7) + ((lane >> 4) << 3)) * P + kk * 32 + ((lane >> 3) & 1) * 16, wb[h][kk]);
+
+  uint8_t* my_ring = ring + warp * kStages * kSlot;
+  uint64_t* my_bars = bars + warp * kStages;
+  uint32_t issued = 0, consumed = 0;
+  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+    const int b = tile / p.blocks_per_img, yb = tile - b * p.blocks_per_img;
+    const int y0 = yb * kC32RB;
+    const int rows_here = min(kC32RB, p.H - y0);
+    const int TR = (rows_here + 2) * p.W;
+    const int flat0 = (b * p.H + y0 - 1) * p.W;               // halo rows may belong to a neighbour image: masked below
+    const int ngroups = (TR + RPB - 1) / RPB;
+    const int n_my = (ngroups - warp + kC32Warps - 1) / kC32Warps;
+    auto issue = [&](int k) {
+      if (lane == 0) {
+        const uint32_t s = issued % kStages;
+        mbar_expect_tx(&my_bars[s], kSlot);
+        tma_load_4d(my_ring + s * kSlot, &tmap, 0, flat0 + (warp + kC32Warps * k) * RPB, 0, 0, &my_bars[s]);
+      }
+      ++issued;
+    };
+    for (int k = 0; k < kStages - 1 && k < n_my; ++k) issue(k);
+    for (int k = 0; k < n_my; ++k) {
+      __syncwarp();
+      if (k + kStages - 1 < n_my) issue(k + kStages - 1);
+      const uint32_t s = consumed % kStages;
+      mbar_wait(&my_bars[s], (consumed / kStages) & 1, 0x43);
+      ++consumed;
+      const uint32_t ta = smem_u32(my_ring + s * kSlot);
+      const int row = lane & 15, hi = lane >> 4;
+#pragma unroll
+      for (int f = 0; f < RPB / 16; ++f) {
+        float acc[2][4];
+#pragma unroll
+        for (int n = 0; n < 2; ++n)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[n][e] = 0.f;
+        const int br = f * 16 + row;                           // row inside the box
+#pragma unroll
+        for (int kk = 0; kk < KS; ++kk) {
+          uint32_t a[4];
+          ldsm_x4(ta + br * P + (((kk * 2 + hi) ^ ((br >> SH) & SWM)) << 4), a);
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            mma_bf16_16816(acc[0], a, wb[h][kk][0], wb[h][kk][1]);
+            mma_bf16_16816(acc[1], a, wb[h][kk][2], wb[h][kk][3]);
+          }
+        }
+        const int r0 = (warp + kC32Warps * k) * RPB + f * 16 + (lane >> 2), r1 = r0 + 8;
+        const int t0 = (lane & 3) * 2;
+        if (r0 < TR) { ds[t0 * p.tr_max + r0] = acc[0][0]; ds[(t0 + 1) * p.tr_max + r0] = acc[0][1]; }
+        if (r1 < TR) { ds[t0 * p.tr_max + r1] = acc[0][2]; ds[(t0 + 1) * p.tr_max + r1] = acc[0][3]; }
+        if (t0 == 0) {
+          if (r0 < TR) ds[8 * p.tr_max + r0] = acc[1][0];
+          if (r1 < TR) ds[8 * p.tr_max + r1] = acc[1][2];
+        }
+      }
+    }
+    __syncthreads();
+    const int npx = rows_here * p.W;
+    for (int i = threadIdx.x; i < npx; i += kC32Threads) {
+      const int y = i / p.W, x = i - y * p.W;
+      float sacc = 0.f;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const int dy = t / 3 - 1, dx = t % 3 - 1;
+        const int yy = y0 + y - dy, xx = x - dx;
+        if (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) sacc += ds[t * p.tr_max + (y + 1 - dy) * p.W + xx];
+      }
+      p.gx[(static_cast<size_t>(b) * p.H + y0 + y) * p.W + x] = sacc;
+    }
+    __syncthreads();
+  }
+}
+
+template <int KS>
+static int d16_dgrad_launch_t(const void* gz, const float* w, float* gx, int B, int H, int W, cudaStream_t st) {
+  constexpr int C = KS * 16, P = KS * 32;
+  D16DgradP p{};
+  p.w = w; p.gx = gx; p.B = B; p.H = H; p.W = W;
+  p.blocks_per_img = (H + kC32RB - 1) / kC32RB;
+  p.n_tiles = B * p.blocks_per_img;
+  p.tr_max = (((kC32RB + 2) * W + 27) / 32) * 32 + 4;     // >= the band, == 4 (mod 32): tap planes 2i land 8 banks apart
+  const long long R = 1LL * B * H * W;
+  if (R > 0x7fffffffLL - 4096) return -1;
+  const size_t smem = 1024 + size_t(kC32Warps) * 4 * 16 * P + 2 * 16 * C * 2 + size_t(9) * p.tr_max * 4 + kC32Warps * 4 * 8;
+  if (smem > 150 * 1024) return -1;
+  CUtensorMap tm;
+  const uint64_t dims[4] = {uint64_t(C), uint64_t(R), 1, 1};
+  const uint32_t box[4] = {uint32_t(C), 16, 1, 1};
+  if (make_tmap_4d_bf16(&tm, gz, dims, box)) return 1;
+  ensure_max_smem(reinterpret_cast<const void*>(d16_dgrad_kernel<KS>), (int)smem);
+  int per_sm = int((224 * 1024) / (smem + 1024)); if (per_sm > 3) per_sm = 3; if (per_sm < 1) per_sm = 1;
+  int grid = per_sm * sm_count(); if (grid > p.n_tiles) grid = p.n_tiles;
+  d16_dgrad_kernel<KS><<<grid, kC32Threads, smem, st>>>(tm, p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error("dl1_dgrad (tensor-core) launch", e);
+  return 0;
+}
+
+// returns -1 when the geometry is not covered (the caller keeps the CUDA-core kernel)
+int d16_dgrad_launch(const void* gz, const float* w, float* gx, int C, int B, int H, int W, cudaStream_t st) {
+  if (W < 4 || H < 1) return -1;
+  if (C == 16) return d16_dgrad_launch_t<1>(gz, w, gx, B, H, W, st);
+  if (C == 32) return d16_dgrad_launch_t<2>(gz, w, gx, B, H, W, st);
+  if (C == 64) return d16_dgrad_launch_t<4>(gz, w, gx, B, H, W, st);
+  return -1;
+}
+
 // x / act / gy: bf16 PNHWC [B][H+1][W+1][64] (channel stride 64, offset 0); fp32 images [B][1][H][W].
 int c32_fwd_launch(const void* x, int B, int H, int W, const float* w, const float* bias, float inv_multiplier,
                    float power, float thres, int training, float* out, float* srs, float* z, cudaStream_t st) {
@@ -320,7 +475,7 @@ int c32_fwd_launch(const void* x, int B, int H, int W, const float* w, const flo
   if (R > 0x7fffffffLL - 4096) return set_error("conv_out: batch too large for 32-bit row indices");
   p.blocks_per_img = (H + kC32RB - 1) / kC32RB;
   p.n_tiles = B * p.blocks_per_img;
-  p.tr_max = (kC32RB + 2) * p.pitch;
+  p.tr_max = (((kC32RB + 2) * p.pitch + 27) / 32) * 32 + 4;   // >= the band, == 4 (mod 32): conflict-free fragment stores
   p.inv_multiplier = inv_multiplier; p.power = power; p.thres = thres; p.training = training;
   const size_t smem = 1024 + size_t(kC32Warps) * kC32FwdStages * 2048 + 16 * 64 * 2 + size_t(9) * p.tr_max * 4 +
                       kC32Warps * kC32FwdStages * 8;

@@ -1050,6 +1050,14 @@ extern "C" int srb_dl1_fwd(const float* img, const float* w, const float* bias, 
 
 extern "C" int srb_dl1_dgrad(const void* gz_bf16, const float* w, float* gx, int C, int B, int H, int W, void* stream) {
   if (!gz_bf16 || !w || !gx) return set_error("dl1_dgrad: null pointer");
+  {
+    static int general = -1;          // SRB_DL1_GENERAL=1: the CUDA-core kernel below (A/B timing, fall-back)
+    if (general < 0) { const char* e = getenv("SRB_DL1_GENERAL"); general = (e && atoi(e) != 0) ? 1 : 0; }
+    if (!general) {
+      const int rc = d16_dgrad_launch(gz_bf16, w, gx, C, B, H, W, (cudaStream_t)stream);
+      if (rc >= 0) return rc;
+    }
+  }
   const long long total = 1LL * B * H * W;
   int grid = ceil_div(total, 256); if (grid > sm_count() * 8) grid = sm_count() * 8;
   cudaStream_t st = (cudaStream_t)stream;
