@@ -98,9 +98,10 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool tma = p.in_f32 == nullptr;
 
+  uint64_t* empty = bars + kDmmaMaxStages;             // "tile consumed by every warp" (TMA path only)
   if (threadIdx.x == 0 && tma) {
     tma_prefetch_desc(&tmap);
-    for (int i = 0; i < p.nst; ++i) mbar_init(&bars[i], 1);
+    for (int i = 0; i < p.nst; ++i) { mbar_init(&bars[i], 1); mbar_init(&empty[i], kDmmaThreads / 32); }
     fence_mbar_init();
   }
   // weights -> shared memory (once per CTA)
@@ -164,12 +165,24 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
     const int img0 = (tile / p.tiles_y) * p.IMGS;
     const int y0 = ty * p.TH;                         // first fragment-grid row of the tile
     const int slot = k % p.nst;
-    __syncthreads();                                  // tile k-1 fully consumed: its buffer takes tile k + nst - 1
-    {
+    if (tma) {
+      // The warps of a CTA share nothing but the source tiles: no block-wide barrier per tile.  Every warp arrives on the
+      // tile's "empty" barrier when it is done with it; only the thread that issues the TMA waits for tile k-1 to be
+      // consumed before its buffer takes tile k + nst - 1, the other warps run ahead by up to nst - 1 tiles.
+      if (threadIdx.x == 0) {
+        const int t = tile + (p.nst - 1) * gridDim.x;
+        if (t < p.n_tiles) {
+          if (k > 0) mbar_wait(&empty[(k - 1) % p.nst], ((k - 1) / p.nst) & 1, 0x31);
+          load_tile(t, (k + p.nst - 1) % p.nst);
+        }
+      }
+      __syncwarp();
+      mbar_wait(&bars[slot], (k / p.nst) & 1, 0x30);
+    } else {
+      __syncthreads();                                // tile k-1 fully consumed: its buffer takes tile k + nst - 1
       const int t = tile + (p.nst - 1) * gridDim.x;
       if (t < p.n_tiles) load_tile(t, (k + p.nst - 1) % p.nst);
     }
-    if (tma) mbar_wait(&bars[slot], (k / p.nst) & 1, 0x30);
     const uint32_t tile_u32 = dsmem_u32(in_s0 + slot * p.tile_bytes);
 
     for (int it = warp; it < NPH * npair; it += kDmmaThreads / 32) {
@@ -359,6 +372,10 @@ dmma_conv_kernel(const DmmaConvP p, const __grid_constant__ CUtensorMap tmap) {
         }
       }
       }
+    }
+    if (tma) {                                        // this warp is done with the tile (its ldmatrix reads are complete)
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[slot]);
     }
   }
 }
@@ -823,7 +840,7 @@ static int dmma_conv_launch_t(DmmaConvP& p, cudaStream_t st) {
   // whose weights alone are too large for that (64 channels: 83 KB) run one CTA per SM with up to 200 KB.  Whatever
   // room is left under the cap goes into more buffers (deeper prefetch), up to kDmmaMaxStages.
   const size_t fixed = size_t(9) * NT * 8 * PP + (NT >= 2 ? size_t(kDmmaThreads / 32) * 32 * (NT * 16 + 16) : 0) +
-                       kDmmaMaxStages * 8 + 1024;
+                       2 * kDmmaMaxStages * 8 + 1024;
   int TH = 0, IMGS = 0, TR = 0, TC = 0, nst = 2;
   size_t smem = 0, tile_bytes = 0;
   bool ok = false;
