@@ -244,15 +244,16 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
 #pragma unroll
     for (int i = 0; i < 8; ++i) y4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
   }
-  uint4* yp = reinterpret_cast<uint4*>(p.y + yrow * p.y_cstride + ycoff + half * 32);
+  // 64 bytes per row and thread: two 256-bit stores (STG.256, sm_100).  A warp's store instruction touches 32 rows either
+  // way; 32 bytes per row make every touched sector a full one and halve the instructions the LSU has to sequence.
+  __nv_bfloat16* yp = p.y + yrow * p.y_cstride + ycoff + half * 32;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    uint4 o;
-    o.x = pack_bf16(v[8 * i], v[8 * i + 1]);
-    o.y = pack_bf16(v[8 * i + 2], v[8 * i + 3]);
-    o.z = pack_bf16(v[8 * i + 4], v[8 * i + 5]);
-    o.w = pack_bf16(v[8 * i + 6], v[8 * i + 7]);
-    yp[i] = o;
+  for (int i = 0; i < 2; ++i) {
+    uint32_t o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = pack_bf16(v[16 * i + 2 * j], v[16 * i + 2 * j + 1]);
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(yp + 16 * i), "r"(o[0]), "r"(o[1]), "r"(o[2]),
+                 "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7]) : "memory");
   }
 }
 
