@@ -51,6 +51,8 @@ int srb_read_fault(unsigned int* fault_out);
  *   store_mode == SRB_STORE_PLAIN  : y[pixel][y_coff + n]
  *   store_mode == SRB_STORE_SHUFFLE: cout = 4*Cy; packed output channel n = (2i+j)*Cy + c goes to
  *                                    y[(2y+i, 2x+j)][y_coff + c]; y has geometry (2H, 2W).
+ * Alignment (SRB_IMPL_TCGEN05): x 16 bytes with x_coff a multiple of 64; y, res1, res2, res3 and y32 - pointer, row pitch
+ * (cstride elements) and channel offset - 32 bytes each: the epilogue moves these per-row streams with 256-bit accesses.
  */
 enum { SRB_ACT_NONE = 0, SRB_ACT_LRELU = 1, SRB_ACT_LRELU_MASK = 2 };
 enum { SRB_STORE_PLAIN = 0, SRB_STORE_SHUFFLE = 1 };

@@ -137,6 +137,17 @@ __device__ __forceinline__ float warp_colsum32(const float (&v)[32], int lane) {
 
 template <bool COHERENT>
 __device__ __forceinline__ uint4 ld_row16(const uint4* p) { return COHERENT ? __ldcg(p) : __ldg(p); }
+// 32 bytes per thread in one instruction (LDG.256, sm_100): the per-row streams of the epilogue are 64 or 128 bytes per
+// thread, each thread on its own row - half the load instructions for the LSU to sequence
+template <bool COHERENT>
+__device__ __forceinline__ void ld_row32(const void* p, uint32_t (&r)[8]) {
+  if (COHERENT)
+    asm volatile("ld.global.cg.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]),
+                 "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "l"(p));
+  else
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]),
+                 "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "l"(p));
+}
 template <bool COHERENT>
 __device__ __forceinline__ float4 ld_row16f(const float4* p) { return COHERENT ? __ldcg(p) : __ldg(p); }
 
@@ -145,22 +156,24 @@ template <bool COHERENT>
 __device__ __forceinline__ void add_residual32(float (&v)[32], const void* base, size_t q, int cstride, int coff, int c0,
                                                float scale, bool f32) {
   if (f32) {
-    const float4* rp = reinterpret_cast<const float4*>(static_cast<const float*>(base) + q * cstride + coff + c0);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float4 u = ld_row16f<COHERENT>(rp + i);
-      v[4 * i] += scale * u.x; v[4 * i + 1] += scale * u.y; v[4 * i + 2] += scale * u.z; v[4 * i + 3] += scale * u.w;
-    }
-  } else {
-    const uint4* rp = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(base) + q * cstride + coff + c0);
+    const float* rp = static_cast<const float*>(base) + q * cstride + coff + c0;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const uint4 u = ld_row16<COHERENT>(rp + i);
-      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+      uint32_t u[8];
+      ld_row32<COHERENT>(rp + 8 * i, u);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        v[8 * i + 2 * j] += scale * bf16lo(w[j]);
-        v[8 * i + 2 * j + 1] += scale * bf16hi(w[j]);
+      for (int j = 0; j < 8; ++j) v[8 * i + j] += scale * __uint_as_float(u[j]);
+    }
+  } else {
+    const __nv_bfloat16* rp = static_cast<const __nv_bfloat16*>(base) + q * cstride + coff + c0;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      uint32_t w[8];
+      ld_row32<COHERENT>(rp + 16 * i, w);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[16 * i + 2 * j] += scale * bf16lo(w[j]);
+        v[16 * i + 2 * j + 1] += scale * bf16hi(w[j]);
       }
     }
   }
@@ -187,7 +200,7 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
     ycoff += n0;
   }
   const int c0 = n0 + half * 32;
-  if (p.bias) {
+  if (p.bias) {                                     // (parameter views: 16-byte alignment only, 128-bit loads)
     const float4* b4 = reinterpret_cast<const float4*>(p.bias + c0);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -240,9 +253,13 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
     p.sign_out[sign_word_index(q, p.sign_cstride, p.sign_coff + (c0 >> 5))] = bits;
   }
   if (EXT && p.y32) {
-    float4* y4 = reinterpret_cast<float4*>(p.y32 + static_cast<size_t>(q) * p.y32_cstride + p.y32_coff + c0);
+    float* y32 = p.y32 + static_cast<size_t>(q) * p.y32_cstride + p.y32_coff + c0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) y4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    for (int i = 0; i < 4; ++i)
+      asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(y32 + 8 * i), "r"(__float_as_uint(v[8 * i])),
+                   "r"(__float_as_uint(v[8 * i + 1])), "r"(__float_as_uint(v[8 * i + 2])), "r"(__float_as_uint(v[8 * i + 3])),
+                   "r"(__float_as_uint(v[8 * i + 4])), "r"(__float_as_uint(v[8 * i + 5])), "r"(__float_as_uint(v[8 * i + 6])),
+                   "r"(__float_as_uint(v[8 * i + 7])) : "memory");
   }
   // 64 bytes per row and thread: two 256-bit stores (STG.256, sm_100).  A warp's store instruction touches 32 rows either
   // way; 32 bytes per row make every touched sector a full one and halve the instructions the LSU has to sequence.
@@ -484,8 +501,16 @@ struct IgemmPlan {
 
 int igemm_check_args(const srb_conv3x3_args* a) {
   if (a->cin % 64 || a->cout % 64 || a->cin <= 0 || a->cout <= 0) return set_error("conv3x3: channels must be multiples of 64");
-  if ((a->x_cstride % 8) || (a->y_cstride % 8) || (a->x_coff % 64) || (a->y_coff % 8))
-    return set_error("conv3x3: channel strides/offsets must keep 16-byte alignment");
+  if ((a->x_cstride % 8) || (a->x_coff % 64))
+    return set_error("conv3x3: input channel stride / offset must keep 16-byte alignment (offset: a multiple of 64)");
+  // the epilogue moves its per-row streams (output, bf16 / fp32 residuals, fp32 copy) with 256-bit accesses
+  auto al32 = [](const void* ptr, int cstride, int coff, int elem) {
+    return ptr == nullptr || (((reinterpret_cast<uintptr_t>(ptr) & 31) == 0) && ((cstride * elem) % 32 == 0) && ((coff * elem) % 32 == 0));
+  };
+  if (!al32(a->y, a->y_cstride, a->y_coff, 2) || !al32(a->res1, a->res1_cstride, a->res1_coff, (a->res_f32 & 1) ? 4 : 2) ||
+      !al32(a->res2, a->res2_cstride, a->res2_coff, (a->res_f32 & 2) ? 4 : 2) ||
+      !al32(a->res3, a->res3_cstride, a->res3_coff, 2) || !al32(a->y32, a->y32_cstride, a->y32_coff, 4))
+    return set_error("conv3x3: output / residual pointers, channel strides and offsets must keep 32-byte alignment");
   if (a->store_mode == SRB_STORE_SHUFFLE && a->cout % 256) return set_error("conv3x3: shuffle store needs cout % 256 == 0");
   const long long R = 1LL * a->batch * (a->H + 1) * (a->W + 1);
   if (R <= 0 || R > 0x7fffffffLL) return set_error("conv3x3: bad geometry");
