@@ -281,6 +281,10 @@ bool conv_t21_enabled();                                                        
 bool conv_t21_plan(const srb_conv3x3_args* a, IgemmPlan* pl);
 int conv3x3_chain21_launch_kernel(const ChainParams& cp, const IgemmPlan& pl, int grid, cudaStream_t stream);
 
+bool conv_pair_enabled();                                                                      // conv_chain2.cu
+bool conv_pair_eligible(const srb_conv3x3_args* a, int n, const IgemmPlan& pl);
+int conv3x3_chain_pair_launch(ChainParams& cp, const srb_conv3x3_args* a, int n, const IgemmPlan& pl, cudaStream_t stream);
+
 size_t conv3x3_chain_flag_bytes(int batch, int H, int W, int n) {
   // sized for the finer tiling (128 rows) so the caller need not know which one the plan picks
   const long long R = 1LL * batch * (H + 1) * (W + 1);
@@ -315,6 +319,9 @@ int conv3x3_chain_launch(const srb_conv3x3_args* a, int n, int* flags, size_t fl
   const int sms = sm_count();
   const int grid = cp.L[0].num_work < sms ? cp.L[0].num_work : sms;
   if (t21) return conv3x3_chain21_launch_kernel(cp, pl, grid, stream);
+  // flags bit 22 forces, bit 23 forbids the CTA-pair kernel (conv_chain2.cu); SRB_CONV_PAIR sets the default
+  if (((a[0].flags & 0x400000) || (conv_pair_enabled() && !(a[0].flags & 0x800000))) && conv_pair_eligible(a, n, pl))
+    return conv3x3_chain_pair_launch(cp, a, n, pl, stream);
   cudaError_t e;
   if (pl.MT == 4) {
     ensure_max_smem(reinterpret_cast<const void*>(conv3x3_chain_kernel<4>), 227 * 1024);

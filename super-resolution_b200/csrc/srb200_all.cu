@@ -16,6 +16,7 @@
 #ifdef SRB_EXPERIMENTAL
 #include "conv_chain21.cu"
 #endif
+#include "conv_chain2.cu"
 #include "wgrad_tc.cu"
 #include "gen_edge.cu"
 #include "disc_fast.cu"

@@ -144,7 +144,8 @@ def _dense_block_layers(ops, L, buf, dst, packs, biases, F_=64, flags=0):
     (2, 80, 80, 2),        # HR geometry: halo of 82 rows, two TMA boxes per window
     (5, 13, 17, 3),        # odd sizes
 ])
-@pytest.mark.parametrize("kflags", [0, 0x100000] if EXPERIMENTAL else [0], ids=["one_tap", "taps_2_1"] if EXPERIMENTAL else ["one_tap"])
+@pytest.mark.parametrize("kflags", [0x800000, 0x400000, 0x100000] if EXPERIMENTAL else [0x800000, 0x400000],
+                         ids=["one_tap", "cta_pair", "taps_2_1"] if EXPERIMENTAL else ["one_tap", "cta_pair"])
 def test_conv3x3_chain_is_bitwise_the_sequential_launches(B, H, W, nblocks, kflags):
     """One chained launch over `nblocks` dense blocks == the same convolutions launched one by one (same kernels, same
     accumulation order: bit-exact), and the sequential result matches torch fp32 on bf16-rounded operands."""
