@@ -310,7 +310,7 @@ int conv3x3_chain_launch(const srb_conv3x3_args* a, int n, int* flags, size_t fl
     if (int rc = igemm_make_plan(&a[0], &pl)) return rc;
   if (n > 1 && flag_bytes < static_cast<size_t>(n) * pl.n_mtiles * sizeof(int))
     return set_error("conv3x3_chain: flag workspace too small (srb_conv3x3_chain_flag_bytes)");
-  if (pl.rows_tile < a[0].W + 2)   // a tile's halo (one image row + 1 pixel) must stay inside its two neighbours
+  if (n > 1 && pl.rows_tile < a[0].W + 2)   // a tile's halo (one image row + 1 pixel) must stay inside its two neighbours
     return set_error("conv3x3_chain: image row wider than a tile");
   ChainParams cp{};
   for (int l = 0; l < n; ++l)

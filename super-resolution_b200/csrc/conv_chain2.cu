@@ -21,9 +21,13 @@
 //   * accumulator-drained (t_empty) lives in the leader: the epilogue warps of both CTAs arrive there (2 x kEpiWarps).
 //   * set-up and tear-down are cluster barriers: no CTA may signal a peer barrier before it is initialised, and no CTA
 //     may free its tensor memory / exit while the pair's MMAs still read its shared memory.
-// Restrictions: cout == 64 (one N tile: the two CTAs of a pair must want the same weights).
+// With cout > 64 a pair takes two M tiles of the SAME 64-wide output slice (the two CTAs must want the same weights).
 // Results are bit-identical to conv_chain.cu (same products, same accumulation order per accumulator).
 #include <stdlib.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
 
 #include "common.cuh"
 #include "sm100.cuh"
@@ -31,7 +35,7 @@
 namespace srb {
 
 #ifndef SRB_CONV_PAIR_DEFAULT
-#define SRB_CONV_PAIR_DEFAULT 0
+#define SRB_CONV_PAIR_DEFAULT 1
 #endif
 
 constexpr int kPairBSlots = 6;                        // weight ring: one slot = this CTA's half of a filter row
@@ -144,8 +148,12 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
 
   const int rows_per_tile = 128 * MT;
   const int n_layers = cp.n_layers;
-  const int n_mtiles = cp.n_mtiles;             // == num_work (one N tile)
-  const int w_first = static_cast<int>(blockIdx.x & ~1u);
+  const int n_mtiles = cp.n_mtiles;
+  const int n_ntiles = cp.L[0].n_ntiles;
+  // pair items: item j = (pair of M tiles j / n_ntiles, N tile j % n_ntiles); pair p takes items p, p + pairs, ...
+  // (n_ntiles == 1: CTA b works on tiles b, b + gridDim.x, ... exactly as in conv_chain.cu)
+  const int n_items = ((n_mtiles + 1) >> 1) * n_ntiles;
+  const int j_first = static_cast<int>(blockIdx.x >> 1), j_step = static_cast<int>(gridDim.x >> 1);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
@@ -158,8 +166,9 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
         const CUtensorMap* tmw = &cp.tw[l];
         if (l + 1 < n_layers) { tma_prefetch_desc(&cp.tx[l + 1]); tma_prefetch_desc(&cp.tw[l + 1]); }
         const int KB = p.KB, x_coff = p.x_coff, cout = p.cout;
-        for (int w0 = w_first; w0 < n_mtiles; w0 += gridDim.x) {
-          const int mt_idx = w0 + static_cast<int>(rank);
+        for (int j = j_first; j < n_items; j += j_step) {
+          const int nt = j % n_ntiles;
+          const int mt_idx = 2 * (j / n_ntiles) + static_cast<int>(rank);
           const bool phantom = mt_idx >= n_mtiles;
           const int q0 = mt_idx * rows_per_tile;
           if (l > 0 && !phantom) {
@@ -181,7 +190,7 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
               if (leader) mbar_expect_tx(&b_full[sb], 2 * kPairBSlotBytes);
               for (int dx = 0; dx < 3; ++dx)
                 tma_load_2d_pair(b_smem + sb * kPairBSlotBytes + dx * kPairBTileBytes, tmw, 0,
-                                 ((dy * 3 + dx) * KB + kb) * cout + static_cast<int>(rank) * 32, b_full_l + sb * 8);
+                                 ((dy * 3 + dx) * KB + kb) * cout + nt * 64 + static_cast<int>(rank) * 32, b_full_l + sb * 8);
               if (++sb == NB) { sb = 0; pb ^= 1; }
             }
           }
@@ -204,7 +213,7 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
       uint32_t sa = 0, pa = 0, sb = 0, pb = 0, as = 0, pt = 0;
       for (int l = 0; l < n_layers; ++l) {
         const int KB = cp.L[l].KB;
-        for (int w0 = w_first; w0 < n_mtiles; w0 += gridDim.x) {
+        for (int j = j_first; j < n_items; j += j_step) {
           mbar_wait_cluster(&t_empty[as], pt ^ 1, 3);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + as * 256 + iss * 64;
@@ -251,13 +260,15 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
       float vs[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) vs[i] = 0.f;
-      if (static_cast<int>(blockIdx.x) < n_mtiles) igemm_prefetch_mask<MT>(p, blockIdx.x, 0, lg, lane, half);
-      for (int w0 = w_first; w0 < n_mtiles; w0 += gridDim.x) {
-        const int mt_idx = w0 + static_cast<int>(rank);
+      if (j_first < n_items)
+        igemm_prefetch_mask<MT>(p, 2 * (j_first / n_ntiles) + static_cast<int>(rank), j_first % n_ntiles, lg, lane, half);
+      for (int j = j_first; j < n_items; j += j_step) {
+        const int nt = j % n_ntiles;
+        const int mt_idx = 2 * (j / n_ntiles) + static_cast<int>(rank);
         const bool phantom = mt_idx >= n_mtiles;
         {
-          const int nw = mt_idx + static_cast<int>(gridDim.x);
-          if (nw < n_mtiles) igemm_prefetch_mask<MT>(p, nw, 0, lg, lane, half);
+          const int nj = j + j_step;      // (a phantom tile's rows are >= R: the prefetch skips them)
+          if (nj < n_items) igemm_prefetch_mask<MT>(p, 2 * (nj / n_ntiles) + static_cast<int>(rank), nj % n_ntiles, lg, lane, half);
         }
         mbar_wait(&t_full[as], pt, 6);
         tc_fence_after();
@@ -284,8 +295,8 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
             }
           }
           if (valid) {
-            if (p.ext) igemm_store_row<true, true>(p, v, q, py, px, 0, half);
-            else igemm_store_row<true, false>(p, v, q, py, px, 0, half);
+            if (p.ext) igemm_store_row<true, true>(p, v, q, py, px, nt, half);
+            else igemm_store_row<true, false>(p, v, q, py, px, nt, half);
           }
           if (p.colsum && valid) {
 #pragma unroll
@@ -330,20 +341,48 @@ static size_t chain_pair_smem_bytes(uint32_t a_stage_bytes) {
 }
 
 bool conv_pair_eligible(const srb_conv3x3_args* a, int n, const IgemmPlan& pl) {
-  if (a[0].cout != 64 || pl.n_mtiles < 2) return false;
+  if (pl.n_mtiles < 2) return false;
   for (int l = 0; l < n; ++l)
     if ((a[l].flags >> 1) & 0x7fff) return false;           // timing-experiment switches exist in conv_igemm.cu only
   return chain_pair_smem_bytes(pl.a_stage_bytes) <= 227 * 1024;
+}
+
+// 2 x cudaOccupancyMaxActiveClusters of the kernel at this shared-memory size, cached per (device, MT, smem)
+static int pair_max_ctas(int MT, size_t smem) {
+  static std::mutex mu;
+  static std::map<std::tuple<int, int, size_t>, int> cache;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lock(mu);
+  auto key = std::make_tuple(dev, MT, smem);
+  auto it = cache.find(key);
+  if (it != cache.end()) return it->second;
+  const void* k = MT == 4 ? reinterpret_cast<const void*>(conv3x3_chain_pair_kernel<4>)
+                : MT == 2 ? reinterpret_cast<const void*>(conv3x3_chain_pair_kernel<2>)
+                          : reinterpret_cast<const void*>(conv3x3_chain_pair_kernel<1>);
+  ensure_max_smem(k, 227 * 1024);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(sm_count() & ~1); cfg.blockDim = dim3(kIgemmThreads); cfg.dynamicSmemBytes = smem;
+  int clusters = 0;
+  cudaError_t e = cudaOccupancyMaxActiveClusters(&clusters, k, &cfg);
+  int v = (sm_count() & ~1);
+  if (e == cudaSuccess && clusters > 0 && 2 * clusters < v) v = 2 * clusters;
+  if (e != cudaSuccess) cudaGetLastError();
+  cache[key] = v;
+  return v;
 }
 
 // cp: filled by conv3x3_chain_launch (tensor maps of the weights still with 64-row boxes; re-encoded here)
 int conv3x3_chain_pair_launch(ChainParams& cp, const srb_conv3x3_args* a, int n, const IgemmPlan& pl, cudaStream_t stream) {
   for (int l = 0; l < n; ++l)
     if (make_tmap_2d_bf16(&cp.tw[l], a[l].w, 64, (uint64_t)9 * (a[l].cin / 64) * a[l].cout, 128, 64, 32)) return 1;
-  const int sms = sm_count() & ~1;
-  const int want = (cp.n_mtiles + 1) & ~1;
-  const int grid = want < sms ? want : sms;
   const size_t smem = chain_pair_smem_bytes(pl.a_stage_bytes);
+  // every CTA of the grid must be able to be resident at once (flag waits between tiles of different CTAs): at most as
+  // many pairs as the device can hold clusters of this kernel (74 on a 148-SM B200: both SMs of every TPC)
+  const int sms = pair_max_ctas(pl.MT, smem);
+  if (sms < 2) return set_error("conv3x3_chain (pair): no resident cluster possible");
+  const int want = ((cp.n_mtiles + 1) >> 1) * cp.L[0].n_ntiles * 2;
+  const int grid = want < sms ? want : sms;
   cudaError_t e;
   if (pl.MT == 4) {
     ensure_max_smem(reinterpret_cast<const void*>(conv3x3_chain_pair_kernel<4>), 227 * 1024);

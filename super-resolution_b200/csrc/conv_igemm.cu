@@ -604,6 +604,8 @@ int igemm_fill(const srb_conv3x3_args* a, const IgemmPlan& pl, IgemmParams* pp, 
 
 bool conv_t21_enabled();                                                                          // conv_chain21.cu
 bool conv_t21_plan(const srb_conv3x3_args* a, struct IgemmPlan* pl);
+bool conv_pair_enabled();                                                                         // conv_chain2.cu
+bool conv_pair_eligible(const srb_conv3x3_args* a, int n, const IgemmPlan& pl);
 int conv3x3_chain_launch(const srb_conv3x3_args* a, int n, int* flags, size_t flag_bytes, cudaStream_t stream);
 
 int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
@@ -612,6 +614,12 @@ int conv3x3_igemm_launch(const srb_conv3x3_args* a, cudaStream_t stream) {
   if (((a->flags & 0x100000) || (conv_t21_enabled() && !(a->flags & 0x200000))) && ((a->flags >> 1) & 0x7fff) == 0) {
     IgemmPlan pl21;
     if (conv_t21_plan(a, &pl21)) return conv3x3_chain_launch(a, 1, nullptr, 0, stream);    // else: image too wide for it
+  }
+  // CTA-pair kernel (conv_chain2.cu): a chain of one layer
+  if (((a->flags & 0x400000) || (conv_pair_enabled() && !(a->flags & 0x800000))) && a->impl == SRB_IMPL_TCGEN05 &&
+      ((a->flags >> 1) & 0x7fff) == 0 && !(a->flags & 0x30000)) {
+    IgemmPlan plp;
+    if (igemm_make_plan(a, &plp) == 0 && conv_pair_eligible(a, 1, plp)) return conv3x3_chain_launch(a, 1, nullptr, 0, stream);
   }
   const bool want_row = (a->flags & 0x10000) || (conv_row_enabled() && !(a->flags & 0x20000));
   if (want_row && ((a->flags >> 1) & 0x7fff) == 0 && !a->colsum && !a->sign_out && !a->mask_bits && !a->res_f32 &&

@@ -12,8 +12,10 @@ TOL = 6e-3
 # srb_conv3x3_args.flags (conv_igemm.cu): bit 16 filter-row kernel, bit 17 one-tap kernel, bit 18 / 19 forbid / force its
 # 512-row tiles (where the geometry fits them; otherwise the 256- or 128-row tiles run)
 # bit 20 / 21 force / forbid the 2+1-tap kernel (conv_chain21.cu)
-KERNELS = {"one_tap": 0x20000 | 0x40000 | 0x200000, "one_tap_512": 0x20000 | 0x80000 | 0x200000, "filter_row": 0x10000 | 0x200000,
-           "taps_2_1": 0x100000}
+# bit 22 / 23 force / forbid the CTA-pair kernel (conv_chain2.cu, cta_group::2)
+KERNELS = {"one_tap": 0x20000 | 0x40000 | 0x200000 | 0x800000, "one_tap_512": 0x20000 | 0x80000 | 0x200000 | 0x800000,
+           "cta_pair": 0x400000 | 0x40000 | 0x200000, "cta_pair_512": 0x400000 | 0x80000 | 0x200000,
+           "filter_row": 0x10000 | 0x200000 | 0x800000, "taps_2_1": 0x100000 | 0x800000}
 
 
 def _experimental_build():
@@ -27,7 +29,7 @@ def _experimental_build():
 
 EXPERIMENTAL = _experimental_build()
 if not EXPERIMENTAL:
-    KERNELS = {k: v for k, v in KERNELS.items() if k in ("one_tap", "one_tap_512")}
+    KERNELS = {k: v for k, v in KERNELS.items() if k in ("one_tap", "one_tap_512", "cta_pair", "cta_pair_512")}
 
 
 def _dev():
