@@ -84,7 +84,10 @@ def traffic_from_profile():
     import glob
     import re
     best = None
-    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_conv3x3_chain*.txt"))):
+    def order(f):       # r<round>_s<session><letter>_...: numeric order (s17 after s9c)
+        m = re.match(r"r(\d+)_s(\d+)([a-z]*)_", os.path.basename(f))
+        return (int(m.group(1)), int(m.group(2)), m.group(3)) if m else (0, 0, "")
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_conv3x3_chain*.txt")), key=order):
         txt = open(f).read()
         m = re.search(r"traffic_bytes_per_launch\s*[:=]\s*([0-9.eE+]+)", txt)
         if m:
@@ -447,8 +450,12 @@ def run_ours(args):
     wg = agg.get("wgrad3x3", [0.0, 1e-9, 0])
     ach = conv[0] / (conv[1] * 1e-3) / 1e12
     chain = G._engine().chain
-    kname = ("conv3x3_chain_kernel (tcgen05 implicit GEMM, %d convolutions per persistent launch in the RRDB trunk) + "
-             "conv3x3_igemm_kernel (remaining layers); fwd + dgrad launches" % chain) if chain else \
+    pair = os.environ.get("SRB_CONV_PAIR", "1") != "0"
+    kname = (("conv3x3_chain_pair_kernel (tcgen05.mma.cta_group::2 implicit GEMM on CTA pairs, %d convolutions per "
+              "persistent launch in the RRDB trunk, single launches for the remaining layers); fwd + dgrad launches" % chain)
+             if pair else
+             ("conv3x3_chain_kernel (tcgen05 implicit GEMM, %d convolutions per persistent launch in the RRDB trunk) + "
+              "conv3x3_igemm_kernel (remaining layers); fwd + dgrad launches" % chain)) if chain else \
         "conv3x3_igemm_kernel (tcgen05 implicit GEMM, fwd + dgrad launches)"
     traffic = traffic_from_profile() if (chain == 5 and args.config == "gan" and B == 512) else None
     roofline = {"bound": "tensor", "kernel": kname,
@@ -462,9 +469,10 @@ def run_ours(args):
                 "wgrad": {"achieved": wg[0] / (wg[1] * 1e-3) / 1e12, "launches_per_step": wg[2],
                           "kernel_ms_per_step": wg[1], "share_of_step": wg[1] / ms,
                           "frac": wg[0] / (wg[1] * 1e-3) / 1e12 / pk["bf16_sustained"]},
-                "ceiling_note": "Cout = 64 makes every MMA 128x64x16: 6 KB of shared-memory operands per 32 tensor "
-                                "clocks = 192 B/clk against 128 B/clk per SM, i.e. 2/3 of the tensor rate at best "
-                                "(48 clk per MMA measured, profiles/r01_s21_mma_rate_probe.txt)",
+                "ceiling_note": "Cout = 64: a 128x64x16 MMA reads 6 KB of shared-memory operands per 32 tensor clocks "
+                                "= 192 B/clk against 128 B/clk per SM (48 clk per MMA measured); on CTA pairs "
+                                "(cta_group::2, weights split) 5 KB per CTA = 40 clk on paper, 43 measured "
+                                "(profiles/r01_s21_mma_rate_probe.txt): 0.74 of the tensor rate at best",
                 "how": "algorithmic FLOPs (2*B*H*W*9*Cin*Cout per launch, summed over a chained launch) / CUDA-event "
                        "time per launch, summed over one instrumented step run right after the timed region"}
     train_flops = world * B * (3 * gf) * 1e9

@@ -75,7 +75,12 @@ typedef struct srb_conv3x3_args {
   const void* res1; int res1_cstride, res1_coff; float res1_scale;
   const void* res2; int res2_cstride, res2_coff; float res2_scale;
   int impl;                    /* SRB_IMPL_* */
-  int flags;                   /* bit0: descriptor base-offset mode (bring-up switch) */
+  int flags;                   /* bit0: descriptor base-offset mode (bring-up switch); bits 1-15: timing-experiment
+                                  switches; bits 16-21: kernel selection of the experimental builds and tile height
+                                  (18 / 19: forbid / force 512-row tiles); bit 22 / 23: force / forbid the CTA-pair
+                                  kernel (csrc/conv_chain2.cu: tcgen05.mma.cta_group::2, thread-block clusters of 2;
+                                  the default for every eligible launch unless SRB_CONV_PAIR=0 is in the environment).
+                                  Every kernel choice gives bit-identical results. */
   void* sign_out;              /* optional uint32 [pixels][sign_cstride]: word sign_coff + (channel / 32) of a pixel gets
                                   bit (channel % 32) = (stored output > 0).  Written next to a LeakyReLU output so that
                                   the input-gradient pass can read LeakyReLU' from 1 bit per element (mask_bits)
