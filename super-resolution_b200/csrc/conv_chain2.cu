@@ -19,6 +19,13 @@
 //   * empty / accumulator-ready barriers exist in both CTAs at the same offset and are signalled by ONE multicast
 //     tcgen05.commit per issuer (mask 0b11).
 //   * accumulator-drained (t_empty) lives in the leader: the epilogue warps of both CTAs arrive there (2 x kEpiWarps).
+//   * release of a finished tile (flags[l][t]) is done by a warp of its own: the epilogue warps arrive on a CTA-local
+//     mbarrier after their stores (st_full, release.cta) and go on with the next tile; warp 13 waits for the eight
+//     arrivals, runs fence.proxy.async + __threadfence() (cumulative: it covers the stores that happen-before it through
+//     the mbarrier, the same pattern as bar.sync + one thread's fence in a grid barrier) and adds kEpiWarps to the flag.
+//     In conv_chain.cu every epilogue warp stalls ~1.6 us per tile in that fence - on the K = 64 / 128 layers, where
+//     the epilogue is the slow side (tools/exp_pair.py, exp_pair_epi.py), that is time of the launch.
+//   * the bias of a layer is staged in shared memory once per layer and warp (igemm_store_row's sbias).
 //   * set-up and tear-down are cluster barriers: no CTA may signal a peer barrier before it is initialised, and no CTA
 //     may free its tensor memory / exit while the pair's MMAs still read its shared memory.
 // With cout > 64 a pair takes two M tiles of the SAME 64-wide output slice (the two CTAs must want the same weights).
@@ -41,6 +48,8 @@ namespace srb {
 constexpr int kPairBSlots = 6;                        // weight ring: one slot = this CTA's half of a filter row
 constexpr int kPairBTileBytes = 32 * 64 * 2;          // 32 output channels x 64 input channels, bf16
 constexpr int kPairBSlotBytes = 3 * kPairBTileBytes;
+constexpr int kPairThreads = kIgemmThreads + 32;      // + warp 13: flag signaller (see "release" below)
+constexpr int kPairTailBytes = 256 + kEpiWarps * 32 * 4 + 256;   // barriers | per-warp bias copies | slack
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -101,7 +110,7 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
 }
 
 template <int MT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kIgemmThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   constexpr int NB = kPairBSlots;
@@ -116,7 +125,10 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
   uint64_t* b_empty = b_full + NB;
   uint64_t* t_full = b_empty + NB;
   uint64_t* t_empty = t_full + 2;               // used in the leader only
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+  uint64_t* st_full = t_empty + 2;              // tile stored by the eight epilogue warps -> signaller
+  uint64_t* st_empty = st_full + 2;             // signaller done with the slot
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(st_empty + 2);
+  float* sbias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [kEpiWarps][32]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -131,6 +143,7 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
     for (int i = 0; i < kAStages; ++i) { mbar_init(&a_full[i], 1); mbar_init(&a_empty[i], kIssuers); }
     for (int i = 0; i < NB; ++i) { mbar_init(&b_full[i], 1); mbar_init(&b_empty[i], kIssuers); }
     for (int i = 0; i < 2; ++i) { mbar_init(&t_full[i], kIssuers); mbar_init(&t_empty[i], 2 * kEpiWarps); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&st_full[i], kEpiWarps); mbar_init(&st_empty[i], 1); }
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -171,7 +184,7 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
           const int mt_idx = 2 * (j / n_ntiles) + static_cast<int>(rank);
           const bool phantom = mt_idx >= n_mtiles;
           const int q0 = mt_idx * rows_per_tile;
-          if (l > 0 && !phantom) {
+          if (l > 0 && !phantom && !(p.dbg & 16)) {
             const int* f = cp.flags + static_cast<size_t>(l - 1) * n_mtiles;
             const int t0 = mt_idx > 0 ? mt_idx - 1 : 0;
             const int t1 = mt_idx + 1 < n_mtiles ? mt_idx + 1 : n_mtiles - 1;
@@ -247,16 +260,15 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
         }
       }
     }
-  } else {
+  } else if (warp < 5 + kEpiWarps) {
     // ------------------------------------------------------------------ epilogue warps 5..12 (both CTAs)
     const int lg = warp & 3;
     const int half = (warp - 5) >> 2;
-    const uint32_t t_empty_l = mapa_u32(smem_u32(t_empty), 0);
-    uint32_t as = 0, pt = 0;
+    uint32_t ct = 0, cs = 0;                     // tiles done / tiles handed to the signaller: ring slot = count & 1,
+                                                 // phase parity = (count >> 1) & 1
     for (int l = 0; l < n_layers; ++l) {
       const IgemmParams& p = cp.L[l];
-      const bool signal = l + 1 < n_layers;
-      int* fl = cp.flags + static_cast<size_t>(l) * n_mtiles;
+      const bool signal = l + 1 < n_layers && !(p.dbg & 16);
       float vs[32];
 #pragma unroll
       for (int i = 0; i < 32; ++i) vs[i] = 0.f;
@@ -270,6 +282,12 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
           const int nj = j + j_step;      // (a phantom tile's rows are >= R: the prefetch skips them)
           if (nj < n_items) igemm_prefetch_mask<MT>(p, 2 * (nj / n_ntiles) + static_cast<int>(rank), nj % n_ntiles, lg, lane, half);
         }
+        if (p.bias && (j == j_first || n_ntiles > 1)) {   // once per layer (and N tile): this warp's 32 bias values
+          __syncwarp();
+          sbias[(warp - 5) * 32 + lane] = __ldg(p.bias + nt * 64 + half * 32 + lane);
+          __syncwarp();
+        }
+        const uint32_t as = ct & 1u, pt = (ct >> 1) & 1u;
         mbar_wait(&t_full[as], pt, 6);
         tc_fence_after();
 #pragma unroll 1
@@ -277,10 +295,13 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
           const int q = mt_idx * rows_per_tile + mt * 128 + lg * 32 + lane;
           const int r = q % p.P;
           const int py = r / p.pitch, px = r - py * p.pitch;
-          const bool valid = !phantom && (q < p.R) && (px < p.W) && (py < p.H);
+          const bool valid = !phantom && (q < p.R) && (px < p.W) && (py < p.H) && !(p.dbg & 4);
           const uint32_t taddr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + as * 256 + mt * (NACC * 64);
           float v[32];
-          {
+          if (p.dbg & 32) {       // timing experiment: no accumulator read-out
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = 0.f;
+          } else {
             uint32_t acc[32];
             tmem_ld32(taddr + half * 32, acc);
             tmem_ld_wait();
@@ -295,8 +316,9 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
             }
           }
           if (valid) {
-            if (p.ext) igemm_store_row<true, true>(p, v, q, py, px, nt, half);
-            else igemm_store_row<true, false>(p, v, q, py, px, nt, half);
+            const float4* sb4 = p.bias ? reinterpret_cast<const float4*>(sbias + (warp - 5) * 32) : nullptr;
+            if (p.ext) igemm_store_row<true, true>(p, v, q, py, px, nt, half, sb4);
+            else igemm_store_row<true, false>(p, v, q, py, px, nt, half, sb4);
           }
           if (p.colsum && valid) {
 #pragma unroll
@@ -305,16 +327,38 @@ conv3x3_chain_pair_kernel(const __grid_constant__ ChainParams cp) {
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(t_empty_l + as * 8);
-        if (signal && !phantom) {
+        if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&t_empty[as]), 0));
+        if (signal && !phantom) {                // hand the tile to the signaller warp (release.cta); no fence here
           fence_proxy_async_all();
-          __threadfence();
           __syncwarp();
-          if (lane == 0) atomicAdd(fl + mt_idx, 1);
+          if (lane == 0) {
+            mbar_wait(&st_empty[cs & 1u], ((cs >> 1) & 1u) ^ 1u, 7);
+            mbar_arrive(&st_full[cs & 1u]);
+          }
+          ++cs;
         }
-        if (++as == 2) { as = 0; pt ^= 1; }
+        ++ct;
       }
       if (p.colsum) atomicAdd(p.colsum + half * 32 + lane, warp_colsum32(vs, lane));
+    }
+  } else {
+    // ------------------------------------------------------------------ warp 13: flag signaller (both CTAs)
+    if (elect_one()) {
+      uint32_t ss = 0, ps = 0;
+      for (int l = 0; l + 1 < n_layers; ++l) {
+        if (cp.L[l].dbg & 16) continue;
+        int* fl = cp.flags + static_cast<size_t>(l) * n_mtiles;
+        for (int j = j_first; j < n_items; j += j_step) {
+          const int mt_idx = 2 * (j / n_ntiles) + static_cast<int>(rank);
+          if (mt_idx >= n_mtiles) continue;      // phantom tile
+          mbar_wait(&st_full[ss], ps, 8);        // the eight epilogue warps have stored their parts of the tile
+          fence_proxy_async_all();
+          __threadfence();
+          atomicAdd(fl + mt_idx, kEpiWarps);
+          mbar_arrive(&st_empty[ss]);
+          if (++ss == 2) { ss = 0; ps ^= 1; }
+        }
+      }
     }
   }
 
@@ -337,13 +381,14 @@ bool conv_pair_enabled() {
 }
 
 static size_t chain_pair_smem_bytes(uint32_t a_stage_bytes) {
-  return 1024 + size_t(kAStages) * a_stage_bytes + size_t(kPairBSlots) * kPairBSlotBytes + 512;
+  return 1024 + size_t(kAStages) * a_stage_bytes + size_t(kPairBSlots) * kPairBSlotBytes + kPairTailBytes;
 }
 
 bool conv_pair_eligible(const srb_conv3x3_args* a, int n, const IgemmPlan& pl) {
   if (pl.n_mtiles < 2) return false;
   for (int l = 0; l < n; ++l)
-    if ((a[l].flags >> 1) & 0x7fff) return false;           // timing-experiment switches exist in conv_igemm.cu only
+    if ((a[l].flags >> 1) & 0x7fff & ~(4 | 16 | 32)) return false;   // timing-experiment switches: only "no epilogue I/O" (4),
+                                                                     // "no flags" (16), "no accumulator read-out" (32) exist here
   return chain_pair_smem_bytes(pl.a_stage_bytes) <= 227 * 1024;
 }
 
@@ -362,7 +407,7 @@ static int pair_max_ctas(int MT, size_t smem) {
                           : reinterpret_cast<const void*>(conv3x3_chain_pair_kernel<1>);
   ensure_max_smem(k, 227 * 1024);
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(sm_count() & ~1); cfg.blockDim = dim3(kIgemmThreads); cfg.dynamicSmemBytes = smem;
+  cfg.gridDim = dim3(sm_count() & ~1); cfg.blockDim = dim3(kPairThreads); cfg.dynamicSmemBytes = smem;
   int clusters = 0;
   cudaError_t e = cudaOccupancyMaxActiveClusters(&clusters, k, &cfg);
   int v = (sm_count() & ~1);
@@ -386,13 +431,13 @@ int conv3x3_chain_pair_launch(ChainParams& cp, const srb_conv3x3_args* a, int n,
   cudaError_t e;
   if (pl.MT == 4) {
     ensure_max_smem(reinterpret_cast<const void*>(conv3x3_chain_pair_kernel<4>), 227 * 1024);
-    e = launch_pdl(conv3x3_chain_pair_kernel<4>, dim3(grid), dim3(kIgemmThreads), smem, stream, cp);
+    e = launch_pdl(conv3x3_chain_pair_kernel<4>, dim3(grid), dim3(kPairThreads), smem, stream, cp);
   } else if (pl.MT == 2) {
     ensure_max_smem(reinterpret_cast<const void*>(conv3x3_chain_pair_kernel<2>), 227 * 1024);
-    e = launch_pdl(conv3x3_chain_pair_kernel<2>, dim3(grid), dim3(kIgemmThreads), smem, stream, cp);
+    e = launch_pdl(conv3x3_chain_pair_kernel<2>, dim3(grid), dim3(kPairThreads), smem, stream, cp);
   } else {
     ensure_max_smem(reinterpret_cast<const void*>(conv3x3_chain_pair_kernel<1>), 227 * 1024);
-    e = launch_pdl(conv3x3_chain_pair_kernel<1>, dim3(grid), dim3(kIgemmThreads), smem, stream, cp);
+    e = launch_pdl(conv3x3_chain_pair_kernel<1>, dim3(grid), dim3(kPairThreads), smem, stream, cp);
   }
   if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) return set_cuda_error("conv3x3_chain (pair) launch", e);

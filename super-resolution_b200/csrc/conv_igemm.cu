@@ -182,9 +182,12 @@ __device__ __forceinline__ void add_residual32(float (&v)[32], const void* base,
 // EXT = false is the round-1 epilogue (bf16 residuals only); EXT = true adds the fp32 residual streams, the third
 // residual, the per-image channel factor and the fp32 output copy.  Two instantiations so that the common layers (four
 // of the five convolutions of a dense block) keep the lean code: the K = 64 / 128 layers are epilogue-bound.
+// sbias: optional shared-memory copy of the 32 bias values this thread's columns need (conv_chain2.cu stages it once per
+// layer: the flag protocol's fences invalidate L1, so a global bias load per row is an L2 round trip on the critical path
+// of the epilogue-bound K = 64 / 128 layers)
 template <bool COHERENT = false, bool EXT = false>
 __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)[32], int q, int py, int px, int nt,
-                                                int half) {
+                                                int half, const float4* sbias = nullptr) {
   const int n0 = nt * 64;
   size_t yrow;
   int ycoff = p.y_coff;
@@ -200,7 +203,13 @@ __device__ __forceinline__ void igemm_store_row(const IgemmParams& p, float (&v)
     ycoff += n0;
   }
   const int c0 = n0 + half * 32;
-  if (p.bias) {                                     // (parameter views: 16-byte alignment only, 128-bit loads)
+  if (sbias) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 b = sbias[i];
+      v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+    }
+  } else if (p.bias) {                              // (parameter views: 16-byte alignment only, 128-bit loads)
     const float4* b4 = reinterpret_cast<const float4*>(p.bias + c0);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
