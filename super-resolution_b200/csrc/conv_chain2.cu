@@ -11,9 +11,10 @@
 // What changes against conv_chain.cu (everything else - tile -> CTA map, flag protocol, epilogue - is that file's):
 //   * CTA rank 0 of a pair (the leader) issues every MMA, for both CTAs; its four issuer threads keep their private
 //     accumulators, which now exist at the same TMEM address in both CTAs (tcgen05.alloc.cta_group::2).
-//   * Tiles: the pair works on tiles (w0, w0 + 1), w0 = (blockIdx.x & ~1) + i * gridDim.x - the same tile -> CTA map
-//     as before.  If the last tile has no partner the peer runs a PHANTOM tile: TMA zero-fills its rows (all out of
-//     bounds), nothing is stored, no flag is touched.
+//   * Tiles: pair p works on items j = p, p + pairs, ...; item j = (M tiles 2 (j / n_ntiles) + {0, 1}, N tile
+//     j % n_ntiles), the CTA of rank r taking the M tile + r.  With one N tile (cout = 64) that is the tile -> CTA map of
+//     conv_chain.cu (CTA b: tiles b, b + gridDim.x, ...).  If the last M tile has no partner the peer runs a PHANTOM
+//     tile: TMA zero-fills its rows (all out of bounds), nothing is stored, no flag is touched.
 //   * full barriers live in the leader: both CTAs' TMA loads (cp.async.bulk.tensor ... .cta_group::2) complete their
 //     bytes on the leader's a_full / b_full, which the leader's producer arms with the bytes of BOTH CTAs.
 //   * empty / accumulator-ready barriers exist in both CTAs at the same offset and are signalled by ONE multicast
